@@ -1,0 +1,80 @@
+"""ctypes binding of libamav_b200.so (C ABI declared in include/amav.h).
+
+There is no CPU fallback: if the shared library is missing or a call fails, this module raises."""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_float, c_int, c_int32, c_int64, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libamav_b200.so")
+
+
+class AmavError(RuntimeError):
+    pass
+
+
+class SplatDims(ctypes.Structure):
+    _fields_ = [("frames", c_int32), ("num_gaussians", c_int32), ("views_per_set", c_int32),
+                ("width", c_int32), ("height", c_int32), ("activate", c_int32), ("scale_modifier", c_float)]
+
+
+_SIGS = {
+    "amav_triplane_project": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
+    "amav_sample_decode": [c_int, c_int, c_int, c_int, c_float] + [c_void_p] * 10 + [c_void_p],
+    "amav_lbs_forward": [c_int, c_int, c_int, c_int] + [c_void_p] * 13 + [c_void_p],
+    "amav_densify_gather": [c_int, c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
+    "amav_splat_preprocess": [ctypes.POINTER(SplatDims)] + [c_void_p] * 12 + [c_void_p],
+    "amav_splat_scan": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_void_p],
+    "amav_splat_bin": [ctypes.POINTER(SplatDims)] + [c_void_p] * 6 + [c_int64, c_void_p, c_void_p],
+    "amav_splat_blend": [ctypes.POINTER(SplatDims)] + [c_void_p] * 4 + [c_int, c_int] + [c_void_p] * 4 + [c_void_p],
+}
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise AmavError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                            "(there is no CPU or PyTorch fallback for the render path)")
+        L = ctypes.CDLL(LIB_PATH)
+        L.amav_last_error.restype = ctypes.c_char_p
+        L.amav_version.restype = c_int
+        L.amav_splat_scan_tmp_elems.restype = c_int64
+        L.amav_splat_scan_tmp_elems.argtypes = [c_int64]
+        for name, sig in _SIGS.items():
+            if hasattr(L, name):
+                fn = getattr(L, name)
+                fn.argtypes = sig
+                fn.restype = c_int
+        _lib = L
+    return _lib
+
+
+def ptr(t):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise AmavError("libamav_b200 takes CUDA tensors only (no CPU path)")
+    if not t.is_contiguous():
+        raise AmavError("tensor must be contiguous")
+    return c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def call(name: str, *args) -> None:
+    fn = getattr(lib(), name, None)
+    if fn is None:
+        raise AmavError(f"{name} is not exported by {LIB_PATH}")
+    rc = fn(*args)
+    if rc != 0:
+        raise AmavError(f"{name} failed ({rc}): {lib().amav_last_error().decode()}")

@@ -1,0 +1,34 @@
+// Shared helpers for libamav_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "amav.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libamav_b200 is written for sm_100a (B200) only"
+#endif
+
+#define AMAV_SM_COUNT 148
+
+void amav_set_error(const char *fmt, ...);
+
+#define AMAV_CHECK_ARG(cond, msg)                                   \
+    do {                                                            \
+        if (!(cond)) {                                              \
+            amav_set_error("%s: %s", __func__, msg);                \
+            return AMAV_EINVAL;                                     \
+        }                                                           \
+    } while (0)
+
+#define AMAV_CHECK_LAUNCH()                                                         \
+    do {                                                                            \
+        cudaError_t e__ = cudaGetLastError();                                       \
+        if (e__ != cudaSuccess) {                                                   \
+            amav_set_error("%s: CUDA error: %s", __func__, cudaGetErrorString(e__)); \
+            return AMAV_ECUDA;                                                      \
+        }                                                                           \
+    } while (0)
+
+static inline int amav_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

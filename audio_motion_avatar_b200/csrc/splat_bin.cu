@@ -1,0 +1,249 @@
+// Stage 4b: binning for all frames of a call, without a global key sort and without a host sync.
+//
+// Upstream (InclusiveSum over Gaussians -> duplicateWithKeys -> 64-bit SortPairs ->
+// identifyTileRanges) sorts D (tile<<32 | depth) keys with ~6 radix passes
+// over HBM.  Here the tile is known when an entry is emitted, so:
+//   1. preprocess already counted entries per tile (tile_count);
+//   2. exclusive scan of tile_count (warp-shuffle scan, 3 small launches) -> tile_start = the
+//      upstream `ranges`, plus D at tile_start[last];
+//   3. scatter: every (Gaussian, tile) pair drops (depth_bits<<32 | gaussian) into its tile's bucket;
+//   4. one CTA per non-empty tile sorts its bucket in shared memory on the 64-bit entry
+//      (depth bits, then Gaussian index: unique keys) and writes the Gaussian indices.
+// The result equals the stable sort of upstream keys: within a tile ascending depth bits, ties in
+// ascending Gaussian index (upstream emits in index order and its radix sort is stable).
+// HBM traffic: D*(8 w + 8 r + 4 w) instead of D*12*2*passes.
+#include "common.cuh"
+
+namespace {
+
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 4;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // 1024 counts per block
+
+__device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) >= o) v += n;
+    }
+    return v;
+}
+
+// Exclusive scan of one value per thread across a 256-thread block; returns the block total in `total`.
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t &total)
+{
+    __shared__ uint32_t warp_sums[SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t inc = warp_inclusive_scan(v);
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+        const uint32_t s = warp_sums[w];
+        if (w < warp) base += s;
+        tot += s;
+    }
+    __syncthreads();
+    total = tot;
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums(const uint32_t *__restrict__ count, int64_t n,
+                                                                 uint32_t *__restrict__ block_sums)
+{
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k)
+        if (base + k < n) s += count[base + k];
+    uint32_t total;
+    block_exclusive_scan(s, total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// Single block: in-place exclusive scan of block_sums[0..nb); block_sums[nb] = grand total.
+__global__ void __launch_bounds__(SCAN_THREADS) scan_spine(uint32_t *block_sums, int nb)
+{
+    uint32_t carry = 0;
+    for (int base = 0; base < nb; base += SCAN_THREADS) {
+        const int i = base + threadIdx.x;
+        const uint32_t v = i < nb ? block_sums[i] : 0u;
+        uint32_t total;
+        const uint32_t ex = block_exclusive_scan(v, total);
+        if (i < nb) block_sums[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) block_sums[nb] = carry;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t *__restrict__ count, int64_t n,
+                                                            const uint32_t *__restrict__ block_sums, int nb,
+                                                            uint32_t *__restrict__ start)
+{
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+    uint32_t c[SCAN_ITEMS];
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        c[k] = base + k < n ? count[base + k] : 0u;
+        s += c[k];
+    }
+    uint32_t total;
+    uint32_t ex = block_exclusive_scan(s, total) + block_sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        if (base + k < n) start[base + k] = ex;
+        ex += c[k];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) start[n] = block_sums[nb];
+}
+
+// One thread per (frame, Gaussian): emit its entries into the tile buckets.
+__global__ void __launch_bounds__(256) scatter_entries(int64_t total, int N, int gx, int tiles,
+                                                        const float4 *__restrict__ geom,
+                                                        const ushort4 *__restrict__ rect,
+                                                        const uint32_t *__restrict__ tile_start,
+                                                        uint32_t *__restrict__ tile_cursor,
+                                                        uint64_t *__restrict__ entries, int64_t capacity,
+                                                        int32_t *overflow)
+{
+    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= total) return;
+    const ushort4 rc = rect[gid];
+    if (rc.z <= rc.x || rc.w <= rc.y) return;
+    const int f = (int)(gid / N);
+    const uint32_t i = (uint32_t)(gid - (int64_t)f * N);
+    const float depth = geom[3 * gid + 2].y;
+    const uint64_t e = ((uint64_t)__float_as_uint(depth) << 32) | (uint64_t)i;
+    const int64_t tbase = (int64_t)f * tiles;
+    for (int y = rc.y; y < rc.w; ++y)
+        for (int x = rc.x; x < rc.z; ++x) {
+            const int64_t t = tbase + y * gx + x;
+            const uint32_t slot = atomicAdd(tile_cursor + t, 1u);
+            const int64_t pos = (int64_t)tile_start[t] + slot;
+            if (pos < capacity) entries[pos] = e;
+            else *overflow = 1;
+        }
+}
+
+// Ascending bitonic sort of n entries (virtual +inf padding to P = next pow2): every
+// compare-exchange moves the minimum to the lower index, so pairs with hi >= n are no-ops.
+template <typename Ptr>
+__device__ __forceinline__ void bitonic_sort(Ptr a, int n, int P)
+{
+    for (int k = 2; k <= P; k <<= 1) {
+        const int hk = k >> 1;
+        for (int i = threadIdx.x; i < (P >> 1); i += blockDim.x) {        // flip step
+            const int blk = i / hk, r = i - blk * hk;
+            const int lo = blk * k + r, hi = blk * k + k - 1 - r;
+            if (hi < n) {
+                const uint64_t x = a[lo], y = a[hi];
+                if (y < x) { a[lo] = y; a[hi] = x; }
+            }
+        }
+        __syncthreads();
+        for (int j = hk >> 1; j >= 1; j >>= 1) {
+            for (int i = threadIdx.x; i < (P >> 1); i += blockDim.x) {
+                const int lo = ((i / j) * (j << 1)) + (i % j), hi = lo + j;
+                if (hi < n) {
+                    const uint64_t x = a[lo], y = a[hi];
+                    if (y < x) { a[lo] = y; a[hi] = x; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_CAP = 8192;     // entries sorted in shared memory (64 KB); larger buckets sort in place in L2/HBM
+
+__global__ void __launch_bounds__(SORT_THREADS) sort_tiles(int64_t num_tiles_total,
+                                                            const uint32_t *__restrict__ tile_start,
+                                                            uint64_t *__restrict__ entries,
+                                                            int32_t *__restrict__ point_list, int64_t capacity)
+{
+    extern __shared__ uint64_t s_ent[];
+    for (int64_t t = blockIdx.x; t < num_tiles_total; t += gridDim.x) {
+        const int64_t s = tile_start[t];
+        int64_t e = tile_start[t + 1];
+        if (e > capacity) e = capacity;
+        const int n = (int)(e - s);
+        if (n <= 0) continue;
+        if (n == 1) {
+            if (threadIdx.x == 0) point_list[s] = (int32_t)(uint32_t)entries[s];
+            continue;
+        }
+        int P = 2;
+        while (P < n) P <<= 1;
+        if (n <= SORT_CAP) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) s_ent[i] = entries[s + i];
+            __syncthreads();
+            bitonic_sort(s_ent, n, P);
+            for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
+            __syncthreads();
+        } else {
+            uint64_t *g = entries + s;
+            __syncthreads();
+            bitonic_sort(g, n, P);
+            for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)g[i];
+            __syncthreads();
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" int64_t amav_splat_scan_tmp_elems(int64_t num_tiles_total)
+{
+    return (num_tiles_total + SCAN_TILE - 1) / SCAN_TILE + 1;
+}
+
+extern "C" int amav_splat_scan(const AmavSplatDims *d, const uint32_t *tile_count, uint32_t *tile_start,
+                               uint32_t *scan_tmp, void *stream_)
+{
+    AMAV_CHECK_ARG(d && d->frames >= 0 && d->width > 0 && d->height > 0, "bad dims");
+    AMAV_CHECK_ARG(tile_count && tile_start && scan_tmp, "null buffer");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int gx = (d->width + 15) / 16, gy = (d->height + 15) / 16;
+    const int64_t nt = (int64_t)d->frames * gx * gy;
+    AMAV_CHECK_ARG(nt < (int64_t)1 << 31, "too many tiles");
+    if (nt == 0) return AMAV_OK;
+    const int nb = amav_div_up(nt, SCAN_TILE);
+    scan_block_sums<<<nb, SCAN_THREADS, 0, stream>>>(tile_count, nt, scan_tmp);
+    scan_spine<<<1, SCAN_THREADS, 0, stream>>>(scan_tmp, nb);
+    scan_apply<<<nb, SCAN_THREADS, 0, stream>>>(tile_count, nt, scan_tmp, nb, tile_start);
+    AMAV_CHECK_LAUNCH();
+    return AMAV_OK;
+}
+
+extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const uint16_t *rect,
+                              const uint32_t *tile_start, uint32_t *tile_cursor, uint64_t *entries,
+                              int32_t *point_list, int64_t capacity, int32_t *overflow, void *stream_)
+{
+    AMAV_CHECK_ARG(d && d->frames >= 0 && d->num_gaussians >= 0, "bad dims");
+    AMAV_CHECK_ARG(tile_start && tile_cursor && overflow, "null buffer");
+    AMAV_CHECK_ARG(capacity >= 0 && (capacity == 0 || (entries && point_list)), "null entries");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int gx = (d->width + 15) / 16, gy = (d->height + 15) / 16;
+    const int tiles = gx * gy;
+    const int64_t nt = (int64_t)d->frames * tiles;
+    const int64_t total = (int64_t)d->frames * d->num_gaussians;
+    if (nt == 0 || total == 0) return AMAV_OK;
+    AMAV_CHECK_ARG(geom && rect, "null geometry");
+    scatter_entries<<<amav_div_up(total, 256), 256, 0, stream>>>(
+        total, d->num_gaussians, gx, tiles, reinterpret_cast<const float4 *>(geom),
+        reinterpret_cast<const ushort4 *>(rect), tile_start, tile_cursor, entries, capacity, overflow);
+    AMAV_CHECK_LAUNCH();
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_CAP * 8);
+        attr_set = true;
+    }
+    const int grid = (int)(nt < AMAV_SM_COUNT * 3 ? nt : AMAV_SM_COUNT * 3);
+    sort_tiles<<<grid, SORT_THREADS, SORT_CAP * 8, stream>>>(nt, tile_start, entries, point_list, capacity);
+    AMAV_CHECK_LAUNCH();
+    return AMAV_OK;
+}

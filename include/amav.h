@@ -1,0 +1,140 @@
+/*
+ * amav.h -- C ABI of libamav_b200.so: the B200 (sm_100a) render path of
+ * liubingqi7/audio-motion-avatar's src/models/renderer.py.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name starts with h_;
+ *   - the caller allocates every input, output and workspace buffer; the library never
+ *     allocates, frees or keeps state between calls (except the last-error string);
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no call synchronises
+ *     the device;
+ *   - return value: 0 on success, negative AMAV_E* on failure; amav_last_error() describes it;
+ *   - F = frames in the call, N = Gaussians per frame, tiles = ceil(W/16)*ceil(H/16);
+ *   - matrices are the 16 floats the reference hands to GaussianRasterizationSettings
+ *     (renderer.py:523-524): already transposed, element (row r, col c) at m[c*4+r].
+ *
+ * Each entry point cites the reference interface it replaces (file:line under the reference repo).
+ */
+#ifndef AMAV_H
+#define AMAV_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AMAV_OK 0
+#define AMAV_EINVAL (-1)   /* bad argument                           */
+#define AMAV_ECUDA (-2)    /* CUDA launch / runtime error            */
+#define AMAV_ECAP (-3)     /* caller-provided capacity too small     */
+
+#define AMAV_TILE 16       /* tile edge in pixels (upstream BLOCK_X/BLOCK_Y) */
+#define AMAV_DEC_OUT 14    /* decoded attributes per Gaussian: xyz3 rot4 scale3 opacity1 shs3 */
+#define AMAV_DEC_PAD 16    /* padded row of the projected triplane */
+
+const char *amav_last_error(void);
+int amav_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Stage 1: triplane projection.  Replaces the channel dimension of F.grid_sample + 5x nn.Linear
+ * (renderer.py:305-312 and :165-171) by projecting the triplane through the decoder heads first
+ * (the decode is linear, so decode(bilinear(T)) == bilinear(decode(T))).
+ *   tokens  [F, C, 3*R*R] fp32, channel-major (renderer.py:85-91: plane p of frame f is
+ *           tokens[f][:, p*R*R:(p+1)*R*R]); frame stride = token_frame_stride floats
+ *   weight  [14, 3+3C] fp32: rows = xyz(3) rot(4) scale(3) opacity(1) shs(3) (renderer.py:51-55)
+ *   proj    [F, 3, R*R, 16] fp32 out: proj[f][p][texel][o] = sum_c weight[o][3+p*C+c]*tokens[f][c][p*R*R+texel]
+ */
+int amav_triplane_project(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
+                          const float *weight, float *proj, void *stream);
+
+/* Stage 2: bilinear query of the projected triplane + xyz/bias terms + construct_gaussians
+ * (renderer.py:292-317, :165-171, :319-346).
+ *   points [F,N,3]  posed, pre-transl sites;  transl [F,3];  weight [14,3+3C]; bias [14]
+ *   outputs (the `gaussians` dict of renderer.py:337-344, each [F,N,k]):
+ *   xyz[3] = points+offset+transl, scale[3] raw, rot[4] normalised (eps 1e-12), opacity[1] raw,
+ *   color[3] = sigmoid(shs).
+ */
+int amav_sample_decode(int F, int N, int C, int R, float radius, const float *proj, const float *points,
+                       const float *transl, const float *weight, const float *bias,
+                       float *xyz, float *scale, float *rot, float *opacity, float *color, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Stage 3: SMPL-X forward (smplx==0.1.28 SMPLX.forward -> lbs.lbs; call site renderer.py:261-274)
+ * for F frames in three launches, and the densify gather (renderer.py:276-288).
+ *   full_pose [F,165] axis-angle incl. pose_mean; shape_comp [F,S] = [betas, expression]
+ *   v_template [V,3]; shapedirs [V,3,S]; J_regressor [J,V]; posedirs [(J-1)*9, 3V];
+ *   parents [J] int32 (parents[0] = -1); lbs_weights [V,J]
+ *   work: v_shaped [F,V,3], joints [F,J,3], pose_feature [F,(J-1)*9], A [F,J,12] (3x4 rel. transforms)
+ *   verts [F,V,3] out (no transl: renderer.py:248-249,271)
+ */
+int amav_lbs_forward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
+                     const float *v_template, const float *shapedirs, const float *J_regressor,
+                     const float *posedirs, const int32_t *parents, const float *lbs_weights,
+                     float *v_shaped, float *joints, float *pose_feature, float *A, float *verts,
+                     void *stream);
+
+/* sites[f][i] = sum_k wgt[i][k] * verts[f][par[i][k]], k < P (flattened SubdivideMeshes levels +
+ * randperm subset, renderer.py:280-288).  P = 1 with wgt = 1 is the plain gather. */
+int amav_densify_gather(int F, int V, int N, int P, const float *verts, const int32_t *par,
+                        const float *wgt, float *sites, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Stage 4: tile-based Gaussian splatting (diff_gaussian_rasterization forward as called at
+ * renderer.py:516-566, batched over frames; no per-frame host sync).
+ */
+typedef struct AmavSplatDims {
+    int32_t frames;          /* F */
+    int32_t num_gaussians;   /* N per Gaussian set */
+    int32_t views_per_set;   /* frame f reads Gaussian set f / views_per_set (render_multi_view, renderer.py:431-445); 1 otherwise */
+    int32_t width, height;
+    int32_t activate;        /* 1: apply render_one's activations (renderer.py:532-533,547) to raw scale/opacity/colour */
+    float scale_modifier;    /* renderer.py:522 (1.0) */
+} AmavSplatDims;
+
+/* 4a  per-Gaussian projection (upstream preprocessCUDA) + per-tile counting.
+ *   view, proj [F,16]; tanfov [F,2] = (tanfovx, tanfovy)
+ *   geom   [F,N,12] fp32: (x, y, -conic.x/2, -conic.y) (-conic.z/2, opacity, r, g) (b, depth, radius, 0)
+ *   rect   [F,N,4] uint16: tile rectangle (minx, miny, maxx, maxy); all zero when culled
+ *   tiles_touched [F,N] int32
+ *   tile_count [F*tiles] uint32: MUST be zeroed by the caller; incremented once per (Gaussian, tile)
+ */
+int amav_splat_preprocess(const AmavSplatDims *d, const float *means3d, const float *scales,
+                          const float *rots, const float *opacities, const float *colors,
+                          const float *view, const float *proj, const float *tanfov,
+                          float *geom, uint16_t *rect, int32_t *tiles_touched, uint32_t *tile_count,
+                          void *stream);
+
+/* 4b  binning.  amav_splat_scan: exclusive scan of tile_count -> tile_start [F*tiles+1]
+ *     (tile_start[last] = D, the number of (Gaussian, tile) entries; the only value the host may
+ *     want to read back, once per call, to size `entries`).  amav_splat_bin: scatter of
+ *     (depth_bits<<32 | gaussian) entries into per-tile buckets + per-tile sort.
+ *     Together equivalent to upstream's InclusiveSum + duplicateWithKeys + SortPairs +
+ *     identifyTileRanges: tile t's sorted run is point_list[tile_start[t] : tile_start[t+1]], ordered
+ *     by (depth bits, Gaussian index) = a stable sort of (tile<<32 | depth) keys.
+ *   scan_tmp   [amav_splat_scan_tmp_elems(F*tiles)] uint32 scratch
+ *   tile_cursor[F*tiles] uint32: MUST be zeroed by the caller
+ *   entries    [capacity] uint64 scratch; point_list [capacity] int32 out (Gaussian index within the frame)
+ *   overflow   [1] int32: set to 1 (and binning truncated) when D > capacity
+ */
+int64_t amav_splat_scan_tmp_elems(int64_t num_tiles_total);
+int amav_splat_scan(const AmavSplatDims *d, const uint32_t *tile_count, uint32_t *tile_start,
+                    uint32_t *scan_tmp, void *stream);
+int amav_splat_bin(const AmavSplatDims *d, const float *geom, const uint16_t *rect,
+                   const uint32_t *tile_start, uint32_t *tile_cursor, uint64_t *entries,
+                   int32_t *point_list, int64_t capacity, int32_t *overflow, void *stream);
+
+/* 4c  blend (upstream renderCUDA) over all tiles of all frames.
+ *   bg [3]; out_color [F,3,H,W] (hwc=0) or [F,H,W,3] (hwc=1, the layout render_batch returns,
+ *   renderer.py:477-479); clamp01=1 applies renderer.py:568.
+ *   final_T [F,H,W], n_contrib [F,H,W] int32, out_invdepth [F,H,W]: each may be NULL (inference).
+ */
+int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
+                     const int32_t *point_list, const float *bg, int hwc, int clamp01,
+                     float *out_color, float *final_T, int32_t *n_contrib, float *out_invdepth,
+                     void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AMAV_H */
