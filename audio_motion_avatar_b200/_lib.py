@@ -25,7 +25,8 @@ class SplatDims(ctypes.Structure):
 _SIGS = {
     "amav_triplane_project": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
     "amav_sample_decode": [c_int, c_int, c_int, c_int, c_float] + [c_void_p] * 10 + [c_void_p],
-    "amav_lbs_forward": [c_int, c_int, c_int, c_int] + [c_void_p] * 13 + [c_void_p],
+    "amav_lbs_precompute": [c_int, c_int, c_int] + [c_void_p] * 7 + [c_void_p],
+    "amav_lbs_forward": [c_int, c_int, c_int, c_int] + [c_void_p] * 14 + [c_void_p],
     "amav_densify_gather": [c_int, c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
     "amav_splat_preprocess": [ctypes.POINTER(SplatDims)] + [c_void_p] * 12 + [c_void_p],
     "amav_splat_scan": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_void_p],

@@ -1,0 +1,239 @@
+// Stages 1+2: triplane query and linear decode (reference src/models/renderer.py:292-317 sample_from_triplane,
+// :165-171 the five nn.Linear heads, :319-346 construct_gaussians).
+//
+// The decode is linear in the sampled features, so decode(bilinear(T)) == bilinear(decode(T)):
+//   1. triplane_project: every texel of every plane is pushed through the decoder heads once
+//      (a [R*R x C] . [C x 14] product per plane, fp32 FMA, HBM-bound: it reads the 25 MB/frame
+//      triplane exactly once and writes 0.8 MB/frame of 16-wide projected texels);
+//   2. sample_decode: per Gaussian site, 3 planes x 4 bilinear taps of 64-byte projected texels
+//      (L2-resident), the xyz/bias terms and construct_gaussians' activations.
+// The reference instead materialises [F,N,1536] sampled features (614 MB/frame) and reads them 5x.
+//
+// Projected texel layout (16 floats, one float4 per lane of a 4-lane group in sample_decode):
+//   slot 0..3  rotation (w,x,y,z)      decoder rows 3..6
+//   slot 4..6  xyz offset, slot 7 opacity   rows 0..2, 10
+//   slot 8..10 scaling, slot 11 = 0         rows 7..9
+//   slot 12..14 shs,    slot 15 = 0         rows 11..13
+#include "common.cuh"
+
+namespace {
+
+__constant__ int c_slot_row[16] = {3, 4, 5, 6, 0, 1, 2, 10, 7, 8, 9, -1, 11, 12, 13, -1};
+
+constexpr int PJ_THREADS = 256;
+constexpr int PJ_TEX = 128;            // texels per CTA (32 lanes x float4)
+constexpr int PJ_KGROUPS = 8;          // one warp per K slice
+
+// smem: w[C][16] (slot-major per channel) then, after the main loop, red[8][128][16] reuses/extends it
+__global__ void __launch_bounds__(PJ_THREADS, 2)
+project_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame_stride,
+               const float *__restrict__ weight, int ldw, float *__restrict__ proj)
+{
+    extern __shared__ float4 s_dyn[];
+    float *s_w = reinterpret_cast<float *>(s_dyn);                   // [C][16]
+    float *s_red = s_w + (size_t)C * 16;                             // [8][14][128]
+    const int tiles_per_plane = R2 / PJ_TEX;
+    const int tile = blockIdx.x % tiles_per_plane;
+    const int p = (blockIdx.x / tiles_per_plane) % 3;
+    const int f = blockIdx.x / (3 * tiles_per_plane);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    for (int i = threadIdx.x; i < C * 16; i += PJ_THREADS) {
+        const int c = i >> 4, s = i & 15;
+        const int row = c_slot_row[s];
+        s_w[i] = row < 0 ? 0.0f : weight[(int64_t)row * ldw + 3 + p * C + c];
+    }
+    __syncthreads();
+
+    const int kper = C / PJ_KGROUPS;
+    const int c0 = warp * kper;
+    const float *src = tokens + (int64_t)f * frame_stride + (int64_t)c0 * (3 * R2) + (int64_t)p * R2 + tile * PJ_TEX + lane * 4;
+    float acc[4][14];
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+#pragma unroll
+        for (int o = 0; o < 14; ++o) acc[t][o] = 0.0f;
+
+    constexpr int U = 8;
+    for (int cb = 0; cb < kper; cb += U) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            v[u] = __ldcs(reinterpret_cast<const float4 *>(src + (int64_t)(cb + u) * (3 * R2)));
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const float4 *wp = reinterpret_cast<const float4 *>(s_w + (size_t)(c0 + cb + u) * 16);
+            const float4 w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+            const float w[14] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y, w2.z, w3.x, w3.y, w3.z};
+            const float tv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+#pragma unroll
+                for (int o = 0; o < 14; ++o) acc[t][o] = fmaf(tv[t], w[o], acc[t][o]);
+        }
+    }
+    // cross-warp (K slice) reduction through shared memory: red[warp][o][texel]
+#pragma unroll
+    for (int o = 0; o < 14; ++o)
+        *reinterpret_cast<float4 *>(s_red + ((size_t)warp * 14 + o) * PJ_TEX + lane * 4) =
+            make_float4(acc[0][o], acc[1][o], acc[2][o], acc[3][o]);
+    __syncthreads();
+    // thread -> (texel, half of the 14 outputs)
+    const int tex = threadIdx.x & (PJ_TEX - 1), half = threadIdx.x >> 7;
+    float r[7];
+#pragma unroll
+    for (int o = 0; o < 7; ++o) r[o] = 0.0f;
+    for (int g = 0; g < PJ_KGROUPS; ++g) {
+#pragma unroll
+        for (int o = 0; o < 7; ++o) r[o] += s_red[((size_t)g * 14 + half * 7 + o) * PJ_TEX + tex];
+    }
+    // compact index 0..13 -> slots (skip 11 and 15)
+    float *out = proj + (((int64_t)f * 3 + p) * R2 + tile * PJ_TEX + tex) * 16;
+    if (half == 0) {
+        reinterpret_cast<float4 *>(out)[0] = make_float4(r[0], r[1], r[2], r[3]);
+        out[4] = r[4]; out[5] = r[5]; out[6] = r[6];
+    } else {
+        out[7] = r[0];
+        reinterpret_cast<float4 *>(out)[2] = make_float4(r[1], r[2], r[3], 0.0f);
+        reinterpret_cast<float4 *>(out)[3] = make_float4(r[4], r[5], r[6], 0.0f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// sample_decode: 4 lanes per Gaussian site, lane l owns float4 slot group l of the projected texel.
+struct SampleParams {
+    int F, N, R;
+    float radius;
+    const float4 *proj;       // [F,3,R*R,4] float4
+    const float *points;      // [F,N,3]
+    const float *transl;      // [F,3]
+    const float *weight, *bias;   // decoder [14,3+3C], [14]
+    int ldw;
+    float *xyz, *scale, *rot, *opacity, *color;
+};
+
+
+__device__ __forceinline__ void tap_coords(float g, int R, int &i0, float &w1)
+{
+    // grid_sample, align_corners=False: i = ((g+1)*R-1)/2
+    const float i = ((g + 1.0f) * (float)R - 1.0f) * 0.5f;
+    const float fl = floorf(i);
+    i0 = (int)fl;
+    w1 = i - fl;
+}
+
+__global__ void __launch_bounds__(256) sample_decode_kernel(const SampleParams p)
+{
+    // per slot: (w_x, w_y, w_z, bias) of the decoder's xyz columns / bias
+    __shared__ float4 s_wb[16];
+    if (threadIdx.x < 16) {
+        const int row = c_slot_row[threadIdx.x];
+        s_wb[threadIdx.x] = row < 0 ? make_float4(0.f, 0.f, 0.f, 0.f)
+                                    : make_float4(p.weight[(int64_t)row * p.ldw], p.weight[(int64_t)row * p.ldw + 1],
+                                                  p.weight[(int64_t)row * p.ldw + 2], p.bias[row]);
+    }
+    __syncthreads();
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t gid = tid >> 2;
+    const int lane4 = (int)(tid & 3);
+    if (gid >= (int64_t)p.F * p.N) return;
+    const int f = (int)(gid / p.N);
+    const float px = p.points[3 * gid], py = p.points[3 * gid + 1], pz = p.points[3 * gid + 2];
+    const float gx = fminf(fmaxf(px / p.radius, -1.0f), 1.0f);
+    const float gy = fminf(fmaxf(py / p.radius, -1.0f), 1.0f);
+    const float gz = fminf(fmaxf(pz / p.radius, -1.0f), 1.0f);
+    const int R = p.R, R2 = R * R;
+    // planes (x,y) (x,z) (y,z): first coordinate indexes W (columns), second H (rows); renderer.py:300-303
+    const float ua[3] = {gx, gx, gy}, va[3] = {gy, gz, gz};
+    const float4 *base = p.proj + ((int64_t)f * 3 * R2) * 4 + lane4;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int pl = 0; pl < 3; ++pl) {
+        int x0, y0;
+        float wx1, wy1;
+        tap_coords(ua[pl], R, x0, wx1);
+        tap_coords(va[pl], R, y0, wy1);
+        const float wx0 = 1.0f - wx1, wy0 = 1.0f - wy1;
+        const float4 *plane = base + (int64_t)pl * R2 * 4;
+        float4 pacc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) {
+                const int xi = x0 + dx, yi = y0 + dy;
+                if (xi >= 0 && xi < R && yi >= 0 && yi < R) {
+                    const float w = (dx ? wx1 : wx0) * (dy ? wy1 : wy0);
+                    const float4 t = __ldg(plane + (int64_t)(yi * R + xi) * 4);
+                    pacc.x = fmaf(t.x, w, pacc.x); pacc.y = fmaf(t.y, w, pacc.y);
+                    pacc.z = fmaf(t.z, w, pacc.z); pacc.w = fmaf(t.w, w, pacc.w);
+                }
+            }
+        acc.x += pacc.x; acc.y += pacc.y; acc.z += pacc.z; acc.w += pacc.w;
+    }
+    // xyz columns of the heads + bias (x = [points, feats], renderer.py:165)
+    float v[4] = {acc.x, acc.y, acc.z, acc.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float4 wb = s_wb[lane4 * 4 + k];
+        v[k] = v[k] + (fmaf(wb.x, px, fmaf(wb.y, py, wb.z * pz)) + wb.w);
+    }
+    if (lane4 == 0) {                      // rot = normalize(rotation), eps 1e-12 (renderer.py:333)
+        const float n = fmaxf(sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3]), 1e-12f);
+        reinterpret_cast<float4 *>(p.rot)[gid] = make_float4(v[0] / n, v[1] / n, v[2] / n, v[3] / n);
+    } else if (lane4 == 1) {               // xyz = points + offset + transl (renderer.py:338); opacity raw
+        const float *t = p.transl + 3 * f;
+        p.xyz[3 * gid] = px + v[0] + t[0];
+        p.xyz[3 * gid + 1] = py + v[1] + t[1];
+        p.xyz[3 * gid + 2] = pz + v[2] + t[2];
+        p.opacity[gid] = v[3];
+    } else if (lane4 == 2) {               // scale raw
+        p.scale[3 * gid] = v[0]; p.scale[3 * gid + 1] = v[1]; p.scale[3 * gid + 2] = v[2];
+    } else {                               // color = sigmoid(shs) (renderer.py:335)
+        p.color[3 * gid] = 1.0f / (1.0f + expf(-v[0]));
+        p.color[3 * gid + 1] = 1.0f / (1.0f + expf(-v[1]));
+        p.color[3 * gid + 2] = 1.0f / (1.0f + expf(-v[2]));
+    }
+}
+
+}  // namespace
+
+extern "C" int amav_triplane_project(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
+                                     const float *weight, float *proj, void *stream)
+{
+    AMAV_CHECK_ARG(F >= 0 && C > 0 && R > 0, "bad dims");
+    AMAV_CHECK_ARG((R * R) % PJ_TEX == 0, "R*R must be a multiple of 128");
+    AMAV_CHECK_ARG(C % (PJ_KGROUPS * 8) == 0, "C must be a multiple of 64");
+    AMAV_CHECK_ARG(token_frame_stride >= (int64_t)C * 3 * R * R, "frame stride too small");
+    if (F == 0) return AMAV_OK;
+    AMAV_CHECK_ARG(tokens && weight && proj, "null buffer");
+    AMAV_CHECK_ARG(((uintptr_t)tokens & 15) == 0 && (token_frame_stride & 3) == 0, "tokens must be 16-byte aligned");
+    const size_t smem = ((size_t)C * 16 + (size_t)PJ_KGROUPS * 14 * PJ_TEX) * sizeof(float);
+    AMAV_CHECK_ARG(smem <= 113 * 1024, "C too large for the shared-memory weight tile");
+    cudaFuncSetAttribute(project_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const int64_t grid = (int64_t)F * 3 * (R * R / PJ_TEX);
+    AMAV_CHECK_ARG(grid < ((int64_t)1 << 31), "too many tiles");
+    project_kernel<<<(unsigned)grid, PJ_THREADS, smem, (cudaStream_t)stream>>>(C, R * R, tokens, token_frame_stride,
+                                                                               weight, 3 + 3 * C, proj);
+    AMAV_CHECK_LAUNCH();
+    return AMAV_OK;
+}
+
+extern "C" int amav_sample_decode(int F, int N, int C, int R, float radius, const float *proj, const float *points,
+                                  const float *transl, const float *weight, const float *bias, float *xyz,
+                                  float *scale, float *rot, float *opacity, float *color, void *stream_)
+{
+    AMAV_CHECK_ARG(F >= 0 && N >= 0 && C > 0 && R > 0 && radius > 0.0f, "bad dims");
+    if ((int64_t)F * N == 0) return AMAV_OK;
+    AMAV_CHECK_ARG(proj && points && transl && weight && bias, "null input");
+    AMAV_CHECK_ARG(xyz && scale && rot && opacity && color, "null output");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SampleParams p;
+    p.F = F; p.N = N; p.R = R; p.radius = radius;
+    p.proj = reinterpret_cast<const float4 *>(proj); p.points = points; p.transl = transl;
+    p.weight = weight; p.bias = bias; p.ldw = 3 + 3 * C;
+    p.xyz = xyz; p.scale = scale; p.rot = rot; p.opacity = opacity; p.color = color;
+    const int64_t threads = (int64_t)F * N * 4;
+    sample_decode_kernel<<<amav_div_up(threads, 256), 256, 0, stream>>>(p);
+    AMAV_CHECK_LAUNCH();
+    return AMAV_OK;
+}

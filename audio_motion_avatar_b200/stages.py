@@ -1,0 +1,142 @@
+"""Host wrappers of stages 1-3 over the C ABI (include/amav.h): SMPL-X forward + densify, triplane
+projection, sample/decode.  Every function takes CUDA fp32 tensors and enqueues on the current stream;
+there is no CPU path."""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr, stream_ptr
+
+POSE_KEYS = ("global_orient", "body_pose", "jaw_pose", "leye_pose", "reye_pose", "left_hand_pose", "right_hand_pose")
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    return t.detach().to(torch.float32).contiguous()
+
+
+class BodyModel:
+    """Device-resident constants of the SMPL-X(-shaped) body model + the once-per-model precompute
+    (amav_lbs_precompute).  Mirrors the buffers of ``smplx.SMPLX`` that the reference builds at
+    renderer.py:206-225: v_template, shapedirs (betas+expression), posedirs, J_regressor, parents,
+    lbs_weights, pose_mean, faces."""
+
+    def __init__(self, model: Dict[str, torch.Tensor], device):
+        dev = torch.device(device)
+        if dev.type != "cuda":
+            raise _lib.AmavError("BodyModel needs a CUDA device (no CPU path)")
+        self.device = dev
+        self.v_template = _f32c(model["v_template"]).to(dev)
+        self.shapedirs = _f32c(model["shapedirs"]).to(dev)
+        self.posedirs = _f32c(model["posedirs"]).to(dev)
+        self.J_regressor = _f32c(model["J_regressor"]).to(dev)
+        self.lbs_weights = _f32c(model["lbs_weights"]).to(dev)
+        self.parents = model["parents"].to(torch.int32).contiguous().to(dev)
+        self.pose_mean = _f32c(model["pose_mean"]).to(dev)
+        self.faces = model.get("faces")
+        self.V = int(self.v_template.shape[0])
+        self.J = int(self.parents.shape[0])
+        self.S = int(self.shapedirs.shape[2])
+        if self.posedirs.shape != ((self.J - 1) * 9, 3 * self.V):
+            raise ValueError(f"posedirs must be [(J-1)*9, 3V], got {tuple(self.posedirs.shape)}")
+        self.J_template = torch.empty(self.J, 3, device=dev)
+        self.J_dirs = torch.empty(self.J, 3, self.S, device=dev)
+        self.weights_T = torch.empty(self.J, self.V, device=dev)
+        call("amav_lbs_precompute", self.V, self.J, self.S, ptr(self.v_template), ptr(self.shapedirs),
+             ptr(self.J_regressor), ptr(self.lbs_weights), ptr(self.J_template), ptr(self.J_dirs),
+             ptr(self.weights_T), stream_ptr())
+
+    def full_pose(self, params: Dict[str, torch.Tensor]) -> Tuple[torch.Tensor, torch.Tensor]:
+        """[F,J*3] axis-angles in smplx.SMPLX.forward's joint order (+ pose_mean) and [F,S] shape
+        coefficients [betas, expression] from the reference's parameter dict (renderer.py:250-258)."""
+        Fr = params["global_orient"].numel() // 3
+        parts = [params[k].reshape(Fr, -1).to(self.device, torch.float32) for k in POSE_KEYS]
+        full = torch.cat(parts, dim=1) + self.pose_mean[None]
+        shape = torch.cat([params["betas"].reshape(Fr, -1), params["expression"].reshape(Fr, -1)], dim=1)
+        return full.contiguous(), shape.to(self.device, torch.float32).contiguous()
+
+
+def lbs_forward(body: BodyModel, full_pose: torch.Tensor, shape_comp: torch.Tensor,
+                return_aux: bool = False):
+    """Posed vertices [F,V,3] without transl (renderer.py:261-274 -> smplx lbs)."""
+    Fr = int(full_pose.shape[0])
+    dev = body.device
+    if full_pose.shape[1] != body.J * 3 or shape_comp.shape[1] != body.S:
+        raise ValueError("full_pose must be [F,J*3] and shape_comp [F,S]")
+    pf = torch.empty(Fr, (body.J - 1) * 9, device=dev)
+    joints = torch.empty(Fr, body.J, 3, device=dev)
+    A = torch.empty(Fr, body.J, 12, device=dev)
+    v_posed = torch.empty(Fr, body.V, 3, device=dev)
+    verts = torch.empty(Fr, body.V, 3, device=dev)
+    call("amav_lbs_forward", Fr, body.V, body.J, body.S, ptr(_f32c(full_pose)), ptr(_f32c(shape_comp)),
+         ptr(body.v_template), ptr(body.shapedirs), ptr(body.posedirs), ptr(body.parents), ptr(body.J_template),
+         ptr(body.J_dirs), ptr(body.weights_T), ptr(pf), ptr(joints), ptr(A), ptr(v_posed), ptr(verts), stream_ptr())
+    if return_aux:
+        return verts, {"pose_feature": pf, "joints": joints, "A": A, "v_posed": v_posed}
+    return verts
+
+
+def densify_gather(verts: torch.Tensor, par: torch.Tensor, wgt: torch.Tensor) -> torch.Tensor:
+    """sites[f,i] = sum_k wgt[i,k] * verts[f, par[i,k]] (flattened SubdivideMeshes levels + subset,
+    renderer.py:276-288).  par int32 [N,P], wgt fp32 [N,P]."""
+    Fr, V = int(verts.shape[0]), int(verts.shape[1])
+    N, P = int(par.shape[0]), int(par.shape[1])
+    sites = torch.empty(Fr, N, 3, device=verts.device)
+    call("amav_densify_gather", Fr, V, N, P, ptr(_f32c(verts)), ptr(par), ptr(wgt), ptr(sites), stream_ptr())
+    return sites
+
+
+def decoder_matrix(decoder) -> Tuple[torch.Tensor, torch.Tensor]:
+    """[14, 3+3C] weight and [14] bias in head order xyz, rotation, scaling, opacity, shs
+    (renderer.py:51-55) from an ``nn.Module`` with ``*_layer`` Linears or a state-dict-like mapping."""
+    names = ("xyz", "rotation", "scaling", "opacity", "shs")
+    if isinstance(decoder, dict):
+        w = [decoder[f"{n}_layer.weight"] for n in names]
+        b = [decoder[f"{n}_layer.bias"] for n in names]
+    else:
+        w = [getattr(decoder, f"{n}_layer").weight for n in names]
+        b = [getattr(decoder, f"{n}_layer").bias for n in names]
+    return torch.cat(w, dim=0), torch.cat(b, dim=0)
+
+
+def triplane_project(tokens: torch.Tensor, weight: torch.Tensor, C: int, R: int,
+                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """tokens [F, C, 3*R*R] (channel-major, renderer.py:85-91; the frame stride may exceed C*3*R*R)
+    -> projected planes [F, 3, R*R, 16]."""
+    if tokens.dim() != 3 or tokens.shape[1] != C or tokens.shape[2] != 3 * R * R:
+        raise ValueError(f"tokens must be [F,{C},{3 * R * R}], got {tuple(tokens.shape)}")
+    if tokens.dtype != torch.float32 or not tokens.is_cuda:
+        raise _lib.AmavError("tokens must be CUDA fp32")
+    if tokens.stride(2) != 1 or tokens.stride(1) != 3 * R * R:
+        tokens = tokens.contiguous()
+    Fr = int(tokens.shape[0])
+    fstride = int(tokens.stride(0)) if Fr > 1 else C * 3 * R * R
+    if out is None:
+        out = torch.empty(Fr, 3, R * R, 16, device=tokens.device)
+    call("amav_triplane_project", Fr, C, R, ctypes_ptr(tokens), fstride, ptr(_f32c(weight)), ptr(out), stream_ptr())
+    return out
+
+
+def ctypes_ptr(t: torch.Tensor):
+    """Device pointer of a tensor whose inner dims are dense but whose outer stride may be padded."""
+    import ctypes
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def sample_decode(proj: torch.Tensor, points: torch.Tensor, transl: torch.Tensor, weight: torch.Tensor,
+                  bias: torch.Tensor, C: int, R: int, radius: float) -> Dict[str, torch.Tensor]:
+    """Bilinear query of the projected planes at ``points`` [F,N,3] + xyz/bias terms + construct_gaussians
+    (renderer.py:292-346).  Returns the reference's ``gaussians`` dict (each [F,N,k]; shs is color)."""
+    Fr, N = int(points.shape[0]), int(points.shape[1])
+    dev = points.device
+    xyz = torch.empty(Fr, N, 3, device=dev)
+    scale = torch.empty(Fr, N, 3, device=dev)
+    rot = torch.empty(Fr, N, 4, device=dev)
+    opacity = torch.empty(Fr, N, 1, device=dev)
+    color = torch.empty(Fr, N, 3, device=dev)
+    call("amav_sample_decode", Fr, N, C, R, float(radius), ptr(proj), ptr(_f32c(points)),
+         ptr(_f32c(transl.reshape(Fr, 3))), ptr(_f32c(weight)), ptr(_f32c(bias)), ptr(xyz), ptr(scale), ptr(rot),
+         ptr(opacity), ptr(color), stream_ptr())
+    return {"xyz": xyz, "scale": scale, "rot": rot, "opacity": opacity, "color": color, "shs": color}

@@ -43,7 +43,9 @@ int amav_version(void);
  *   tokens  [F, C, 3*R*R] fp32, channel-major (renderer.py:85-91: plane p of frame f is
  *           tokens[f][:, p*R*R:(p+1)*R*R]); frame stride = token_frame_stride floats
  *   weight  [14, 3+3C] fp32: rows = xyz(3) rot(4) scale(3) opacity(1) shs(3) (renderer.py:51-55)
- *   proj    [F, 3, R*R, 16] fp32 out: proj[f][p][texel][o] = sum_c weight[o][3+p*C+c]*tokens[f][c][p*R*R+texel]
+ *   proj    [F, 3, R*R, 16] fp32 out: proj[f][p][texel][slot] = sum_c weight[row(slot)][3+p*C+c]*tokens[f][c][p*R*R+texel]
+ *           slots: 0..3 rotation (rows 3..6), 4..6 xyz (rows 0..2), 7 opacity (row 10), 8..10 scaling (rows 7..9),
+ *           12..14 shs (rows 11..13), 11 and 15 zero.  C % 64 == 0, (R*R) % 128 == 0.
  */
 int amav_triplane_project(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
                           const float *weight, float *proj, void *stream);
@@ -62,17 +64,26 @@ int amav_sample_decode(int F, int N, int C, int R, float radius, const float *pr
 /* ---------------------------------------------------------------------------------------------
  * Stage 3: SMPL-X forward (smplx==0.1.28 SMPLX.forward -> lbs.lbs; call site renderer.py:261-274)
  * for F frames in three launches, and the densify gather (renderer.py:276-288).
- *   full_pose [F,165] axis-angle incl. pose_mean; shape_comp [F,S] = [betas, expression]
- *   v_template [V,3]; shapedirs [V,3,S]; J_regressor [J,V]; posedirs [(J-1)*9, 3V];
- *   parents [J] int32 (parents[0] = -1); lbs_weights [V,J]
- *   work: v_shaped [F,V,3], joints [F,J,3], pose_feature [F,(J-1)*9], A [F,J,12] (3x4 rel. transforms)
+ *
+ * amav_lbs_precompute: once per body model (renderer.py:206-225 builds the model once too).
+ *   v_template [V,3]; shapedirs [V,3,S]; J_regressor [J,V]; lbs_weights [V,J]
+ *   out: J_template [J,3] = J_regressor.v_template; J_dirs [J,3,S] = J_regressor.shapedirs
+ *        (so joints = J_template + J_dirs.shape = J_regressor.v_shaped); weights_T [J,V].
+ * amav_lbs_forward:
+ *   full_pose [F,J*3] axis-angle incl. pose_mean, joint order of smplx.SMPLX.forward;
+ *   shape_comp [F,S] = [betas, expression]; posedirs [(J-1)*9, 3V]; parents [J] int32 (parents[0] = -1)
+ *   work: pose_feature [F,(J-1)*9], joints [F,J,3], A [F,J,12] (3x4 relative transforms, 16-byte aligned),
+ *         v_posed [F,V,3]
  *   verts [F,V,3] out (no transl: renderer.py:248-249,271)
  */
+int amav_lbs_precompute(int V, int J, int S, const float *v_template, const float *shapedirs,
+                        const float *J_regressor, const float *lbs_weights, float *J_template,
+                        float *J_dirs, float *weights_T, void *stream);
 int amav_lbs_forward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
-                     const float *v_template, const float *shapedirs, const float *J_regressor,
-                     const float *posedirs, const int32_t *parents, const float *lbs_weights,
-                     float *v_shaped, float *joints, float *pose_feature, float *A, float *verts,
-                     void *stream);
+                     const float *v_template, const float *shapedirs, const float *posedirs,
+                     const int32_t *parents, const float *J_template, const float *J_dirs,
+                     const float *weights_T, float *pose_feature, float *joints, float *A, float *v_posed,
+                     float *verts, void *stream);
 
 /* sites[f][i] = sum_k wgt[i][k] * verts[f][par[i][k]], k < P (flattened SubdivideMeshes levels +
  * randperm subset, renderer.py:280-288).  P = 1 with wgt = 1 is the plain gather. */
