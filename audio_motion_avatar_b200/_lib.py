@@ -46,6 +46,7 @@ def lib() -> ctypes.CDLL:
         L = ctypes.CDLL(LIB_PATH)
         L.amav_last_error.restype = ctypes.c_char_p
         L.amav_version.restype = c_int
+        L.amav_launch_count.restype = c_int64
         L.amav_splat_scan_tmp_elems.restype = c_int64
         L.amav_splat_scan_tmp_elems.argtypes = [c_int64]
         for name, sig in _SIGS.items():
@@ -72,10 +73,49 @@ def stream_ptr():
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+class StageTimer:
+    """CUDA-event timing of every C-ABI call made while it is installed (``with StageTimer() as t``); events are
+    recorded on the current stream around each call, resolved by ``summary()`` after a synchronize."""
+
+    def __init__(self):
+        self.events = []
+
+    def __enter__(self):
+        global _TIMER
+        self._prev, _TIMER = _TIMER, self
+        return self
+
+    def __exit__(self, *exc):
+        global _TIMER
+        _TIMER = self._prev
+
+    def summary(self):
+        torch.cuda.synchronize()
+        out = {}
+        for name, a, b in self.events:
+            ms, n = out.get(name, (0.0, 0))
+            out[name] = (ms + a.elapsed_time(b), n + 1)
+        return out
+
+
+_TIMER = None
+
+
+def launch_count() -> int:
+    return int(lib().amav_launch_count())
+
+
 def call(name: str, *args) -> None:
     fn = getattr(lib(), name, None)
     if fn is None:
         raise AmavError(f"{name} is not exported by {LIB_PATH}")
-    rc = fn(*args)
+    if _TIMER is not None:
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        rc = fn(*args)
+        b.record()
+        _TIMER.events.append((name, a, b))
+    else:
+        rc = fn(*args)
     if rc != 0:
         raise AmavError(f"{name} failed ({rc}): {lib().amav_last_error().decode()}")

@@ -13,6 +13,7 @@
 #define AMAV_SM_COUNT 148
 
 void amav_set_error(const char *fmt, ...);
+void amav_count_launches(int n);
 
 #define AMAV_CHECK_ARG(cond, msg)                                   \
     do {                                                            \
@@ -29,6 +30,7 @@ void amav_set_error(const char *fmt, ...);
             amav_set_error("%s: CUDA error: %s", __func__, cudaGetErrorString(e__)); \
             return AMAV_ECUDA;                                                      \
         }                                                                           \
+        amav_count_launches(1);                                                     \
     } while (0)
 
 static inline int amav_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

@@ -300,6 +300,7 @@ extern "C" int amav_lbs_forward(int F, int V, int J, int S, const float *full_po
     AMAV_CHECK_ARG(F <= 65535, "F too large for one call");
     dim3 gs(amav_div_up(V, 256), F);
     skin_kernel<<<gs, 256, 0, stream>>>(V, J, weights_T, A, v_posed, verts);
+    amav_count_launches(2);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }

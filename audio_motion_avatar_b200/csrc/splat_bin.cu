@@ -215,6 +215,7 @@ extern "C" int amav_splat_scan(const AmavSplatDims *d, const uint32_t *tile_coun
     scan_block_sums<<<nb, SCAN_THREADS, 0, stream>>>(tile_count, nt, scan_tmp);
     scan_spine<<<1, SCAN_THREADS, 0, stream>>>(scan_tmp, nb);
     scan_apply<<<nb, SCAN_THREADS, 0, stream>>>(tile_count, nt, scan_tmp, nb, tile_start);
+    amav_count_launches(2);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }

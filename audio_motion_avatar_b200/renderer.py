@@ -1,0 +1,349 @@
+"""Drop-in for the reference's ``src/models/renderer.py`` (liubingqi7/audio-motion-avatar): same names,
+argument meaning and return shapes -- ``Renderer``, ``render_batch``, ``render_one``, ``render_multi_view``,
+``SCALE_BIAS``, ``OPACITY_BIAS``, ``SUBDEVIDE_VERTS`` -- on top of libamav_b200.so.
+
+Differences from the reference, all deliberate:
+* all frames of a call go through ONE batched pass per stage (no Python loop over frames, renderer.py:475-477;
+  no per-frame host sync, renderer.py:504-505 / graphic_utils.py:124-125);
+* the triplane is projected through the linear heads before it is sampled (fact 5) instead of materialising
+  [F,N,1536] features;
+* the PTv3 point encoder/refiner (renderer.py:34-47,143-151) is bypassed: its last layer is zero-initialised so
+  it is an exact no-op at random init, and spconv is not available; the conv triplane upsampler is not built;
+* ``cfg.num_gaussians`` (optional) overrides SUBDEVIDE_VERTS so 100k/500k sites are possible;
+* there is no CPU path: tensors are moved to ``cfg.device`` (a CUDA device) and errors are raised otherwise.
+"""
+from __future__ import annotations
+
+import math
+import warnings
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib, stages, synthetic
+from .splat import SplatWorkspace, splat_forward
+
+SUBDEVIDE_VERTS = {0: 10000, 1: 30000, 2: 30000}      # renderer.py:14-18 (sic)
+SCALE_BIAS = 3.9                                        # renderer.py:428
+OPACITY_BIAS = 0.0                                      # renderer.py:429
+ZNEAR, ZFAR = 0.01, 100.0                               # renderer.py:492-493
+
+
+def inverse_sigmoid(x: float) -> float:
+    """src/utils/math_utils.py:7-11."""
+    return math.log(x / (1.0 - x))
+
+
+# ------------------------------------------------------------------------------------------------
+# camera set-up of render_one (renderer.py:486-510; graphic_utils.py:67-78,103-136,144-145), batched
+# ------------------------------------------------------------------------------------------------
+def camera_matrices(K: torch.Tensor, E: torch.Tensor, height: int, width: int):
+    """K [F,3,3], E [F,4,4] on the device -> (viewmatrix [F,4,4], projmatrix [F,4,4], tanfov [F,2]) exactly as
+    render_one hands them to GaussianRasterizationSettings (already transposed), without a host sync.
+
+    The reference builds Rt = E, inverts it twice (getWorld2View2_torch), forms K_ndc from Python floats
+    (double precision) and takes math.tan of the fp32 half-angle in double; the same operations are done
+    here batched: two ``torch.linalg.inv``, double arithmetic for K_ndc and tan, then a cast to fp32."""
+    K = K.reshape(-1, 3, 3).float()
+    E = E.reshape(-1, 4, 4).float()
+    Fr = K.shape[0]
+    dev = K.device
+    Rt = torch.zeros(Fr, 4, 4, device=dev)
+    Rt[:, :3, :3] = E[:, :3, :3]
+    Rt[:, :3, 3] = E[:, :3, 3]
+    Rt[:, 3, 3] = 1.0
+    view = torch.linalg.inv(torch.linalg.inv(Rt)).transpose(1, 2)
+    fx, fy, cx, cy = K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2]
+    fovx = 2 * torch.atan(width / (2 * fx))
+    fovy = 2 * torch.atan(height / (2 * fy))
+    tanfov = torch.stack([torch.tan((fovx * 0.5).double()), torch.tan((fovy * 0.5).double())], dim=1).float()
+    fxd, fyd, cxd, cyd = fx.double(), fy.double(), cx.double(), cy.double()
+    Kn = torch.zeros(Fr, 4, 4, dtype=torch.float64, device=dev)
+    Kn[:, 0, 0] = 2 * fxd / width
+    Kn[:, 0, 2] = (2 * cxd - width) / width
+    Kn[:, 1, 1] = 2 * fyd / height
+    Kn[:, 1, 2] = (2 * cyd - height) / height
+    Kn[:, 2, 2] = ZFAR / (ZFAR - ZNEAR)
+    Kn[:, 2, 3] = -ZFAR * ZNEAR / (ZFAR - ZNEAR)
+    Kn[:, 3, 2] = 1.0
+    proj = Kn.float().transpose(1, 2)
+    full = torch.bmm(view, proj)
+    return view.contiguous(), full.contiguous(), tanfov.contiguous()
+
+
+def _background(bg_color, device) -> torch.Tensor:
+    if bg_color is None:
+        bg_color = [1, 1, 1]
+    if isinstance(bg_color, torch.Tensor):
+        return bg_color.to(device, torch.float32).reshape(3)
+    return torch.tensor(list(bg_color), dtype=torch.float32, device=device)
+
+
+_WORKSPACES: Dict[int, SplatWorkspace] = {}
+
+
+def _workspace(device) -> SplatWorkspace:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    ws = _WORKSPACES.get(idx)
+    if ws is None:
+        ws = _WORKSPACES[idx] = SplatWorkspace()
+    return ws
+
+
+def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug, views_per_set, hwc):
+    """All frames of a call in one batched splat pass.  Gaussian tensors [G,N,k] (pre-activation scale and
+    opacity as in the reference's ``gaussians`` dict), cameras [G*views_per_set,...]."""
+    if not getattr(args, "rgb", True):
+        # renderer.py:541-545 feeds 3-channel colours to eval_sh(sh_degree=3), which asserts on the coefficient
+        # count (graphic_utils.py:722): the branch is dead in the reference too.
+        raise ValueError("args.rgb=False (SH colours) is not supported: the reference's own SH branch asserts "
+                         "for 3-channel colours; use rgb=True")
+    dev = xyz.device
+    if dev.type != "cuda":
+        raise _lib.AmavError("rendering needs CUDA tensors (no CPU path)")
+    height, width = int(args.image_size[0]), int(args.image_size[1])
+    view, full, tanfov = camera_matrices(K.to(dev), E.to(dev), height, width)
+    bg = _background(bg_color, dev)
+    activate = True
+    if debug:                                        # renderer.py:535-537
+        scale = torch.full_like(scale, 0.01)
+        opacity = torch.full_like(opacity, 0.1)
+        color = color.clamp(0.0, 1.0)
+        activate = False
+    out = splat_forward(xyz, scale, rot, opacity, color, view, full, tanfov, bg, height, width,
+                        views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=True,
+                        workspace=_workspace(dev))
+    return out["color"]
+
+
+def render_batch(gaussians, K, E, args, bg_color=None, debug=False):
+    """renderer.py:447-479.  gaussians: dict of [B*T,N,k]; K [B,T,3,3]; E [B,T,4,4] -> [B,T,H,W,3] in [0,1]."""
+    B, T = E.shape[0], E.shape[1]
+    g = lambda k, d: gaussians[k].reshape(B * T, -1, d).float()
+    img = _render_frames(g("xyz", 3), g("rot", 4), g("scale", 3), g("opacity", 1), g("color", 3),
+                         K.reshape(-1, 3, 3), E.reshape(-1, 4, 4), args, bg_color, debug, 1, True)
+    return img.reshape(B, T, int(args.image_size[0]), int(args.image_size[1]), 3)
+
+
+def render_multi_view(gaussians, K, E, args, bg_color=None, debug=False):
+    """renderer.py:431-445.  gaussians [B,N,k] rendered from T views each, without the reference's T-fold
+    ``expand().reshape()`` copies: frame f reads Gaussian set f // T."""
+    B, T = E.shape[0], E.shape[1]
+    g = lambda k, d: gaussians[k].reshape(B, -1, d).float()
+    img = _render_frames(g("xyz", 3), g("rot", 4), g("scale", 3), g("opacity", 1), g("color", 3),
+                         K.reshape(-1, 3, 3), E.reshape(-1, 4, 4), args, bg_color, debug, T, True)
+    return img.reshape(B, T, int(args.image_size[0]), int(args.image_size[1]), 3)
+
+
+def render_one(xyzs, rots, scales, opacities, colors, K, E, args, bg_color=None, debug=False):
+    """renderer.py:481-570: one frame, returns [3,H,W] clamped to [0,1]."""
+    img = _render_frames(xyzs[None].float(), rots[None].float(), scales[None].float(), opacities[None].float(),
+                         colors[None].float(), K[None], E[None], args, bg_color, debug, 1, False)
+    return img[0]
+
+
+# ------------------------------------------------------------------------------------------------
+# body model loading (what smplx.SMPLX(model_path, ...) does at renderer.py:206-225)
+# ------------------------------------------------------------------------------------------------
+def load_smplx_model(path: str, num_betas: int = 10, num_expression_coeffs: int = 10,
+                     flat_hand_mean: bool = False) -> Dict[str, torch.Tensor]:
+    """Read ``SMPLX_NEUTRAL.npz`` (the file smplx==0.1.28 loads; ``path`` may be the model folder, a
+    ``smplx`` sub-folder or the file) into the buffer dict used by ``stages.BodyModel``:
+    shapedirs = [shape basis[:num_betas], expression basis[:num_expression_coeffs]] (smplx keeps the
+    expression basis at offset 300), posedirs reshaped to [(J-1)*9, 3V], parents from kintree_table[0]
+    with parents[0] = -1, pose_mean = zeros except the hand means unless ``flat_hand_mean``."""
+    import os
+    cands = [path, os.path.join(path, "SMPLX_NEUTRAL.npz"), os.path.join(path, "smplx", "SMPLX_NEUTRAL.npz")]
+    file = next((c for c in cands if os.path.isfile(c)), None)
+    if file is None:
+        raise FileNotFoundError(f"no SMPL-X model file under {path!r} (looked for SMPLX_NEUTRAL.npz)")
+    d = np.load(file, allow_pickle=True)
+    V = d["v_template"].shape[0]
+    sd = np.asarray(d["shapedirs"], dtype=np.float32)
+    shape_basis = sd[:, :, :num_betas]
+    expr_basis = sd[:, :, 300:300 + num_expression_coeffs]
+    posedirs = np.asarray(d["posedirs"], dtype=np.float32).reshape(V * 3, -1).T
+    parents = np.asarray(d["kintree_table"][0], dtype=np.int64).copy()
+    parents[0] = -1
+    J = parents.shape[0]
+    pose_mean = np.zeros(J * 3, dtype=np.float32)
+    if not flat_hand_mean:
+        pose_mean[25 * 3:40 * 3] = np.asarray(d["hands_meanl"], dtype=np.float32).reshape(-1)
+        pose_mean[40 * 3:55 * 3] = np.asarray(d["hands_meanr"], dtype=np.float32).reshape(-1)
+    return {
+        "v_template": torch.from_numpy(np.asarray(d["v_template"], dtype=np.float32)),
+        "faces": torch.from_numpy(np.asarray(d["f"], dtype=np.int64)),
+        "shapedirs": torch.from_numpy(np.ascontiguousarray(np.concatenate([shape_basis, expr_basis], axis=2))),
+        "posedirs": torch.from_numpy(np.ascontiguousarray(posedirs)),
+        "J_regressor": torch.from_numpy(np.asarray(d["J_regressor"], dtype=np.float32)),
+        "parents": torch.from_numpy(parents),
+        "lbs_weights": torch.from_numpy(np.asarray(d["weights"], dtype=np.float32)),
+        "pose_mean": torch.from_numpy(pose_mean),
+    }
+
+
+class _Decoder(nn.Module):
+    pass
+
+
+class Renderer(nn.Module):
+    """renderer.py:20-346.  ``Renderer(cfg, smpl_decoder=None, body_model=None)``; ``body_model`` (a buffer dict as
+    from ``synthetic.make_body_model`` / ``load_smplx_model``) replaces ``cfg.smplx_model_path`` when no SMPL-X
+    file is available."""
+
+    def __init__(self, cfg=None, smpl_decoder=None, body_model: Optional[Dict[str, torch.Tensor]] = None):
+        super().__init__()
+        self.cfg = cfg
+        dev = torch.device(getattr(cfg, "device", "cuda"))
+        if dev.type != "cuda":
+            raise _lib.AmavError("Renderer needs cfg.device to be a CUDA device (no CPU path)")
+        _lib.lib()                                   # fail loudly now if the extension is missing
+        self._device = dev
+        if body_model is None:
+            body_model = load_smplx_model(cfg.smplx_model_path, 10, cfg.num_expression_coeffs,
+                                          bool(getattr(cfg, "flat_hand_mean", False)))
+        self.smplx_model = stages.BodyModel(body_model, dev)
+        steps = int(getattr(cfg, "subdivide_steps", 2))
+        self.num_verts = int(getattr(cfg, "num_gaussians", 0) or SUBDEVIDE_VERTS[steps])
+        self._dense_par = self._dense_wgt = None
+        if getattr(cfg, "densify_smplx_verts", False):
+            self.init_smplx_subdivider(subdivide_steps=steps)
+        if getattr(cfg, "predict_smplx_params", False):
+            self.smpl_decoder = smpl_decoder
+        else:
+            self.smpl_decoder = None                 # the reference leaves it unset and crashes at :104
+        if getattr(cfg, "upsample_triplane", False):
+            raise NotImplementedError("upsample_triplane is outside the render path built here (SURVEY.md a-13); "
+                                      "hand the renderer a ready triplane and set upsample_triplane: false")
+        if not getattr(cfg, "no_point_refiner", True):
+            warnings.warn("point_encoder/point_refiner (PTv3) are bypassed: zero-initialised last layer makes them an "
+                          "exact no-op at random init; trained refiner weights are ignored", stacklevel=2)
+        C = int(cfg.triplane_feature_dim)
+        dec = _Decoder()
+        dec.xyz_layer = nn.Linear(C * 3 + 3, 3)
+        dec.rotation_layer = nn.Linear(C * 3 + 3, 4)
+        dec.scaling_layer = nn.Linear(C * 3 + 3, 3)
+        dec.opacity_layer = nn.Linear(C * 3 + 3, 1)
+        dec.shs_layer = nn.Linear(C * 3 + 3, 3)
+        for layer in (dec.xyz_layer, dec.rotation_layer, dec.scaling_layer, dec.opacity_layer, dec.shs_layer):
+            nn.init.constant_(layer.weight, 0)
+            nn.init.constant_(layer.bias, 0)
+        with torch.no_grad():                        # renderer.py:57-71
+            dec.rotation_layer.bias[0] = 1.0
+            dec.scaling_layer.bias.fill_(-1.0)
+            dec.opacity_layer.bias.fill_(inverse_sigmoid(0.1))
+        self.gaussian_decoder = dec.to(dev)
+        self._fixed_idx = None
+
+    # -- densify table (renderer.py:227-243) ------------------------------------------------------
+    def init_smplx_subdivider(self, subdivide_steps=2):
+        """The reference keeps ``max(1, subdivide_steps)`` SubdivideMeshes objects; here the levels are
+        flattened once into a (parents, weights) table over the base vertices."""
+        levels = max(1, int(subdivide_steps))
+        faces = self.smplx_model.faces
+        faces = faces.cpu().numpy() if isinstance(faces, torch.Tensor) else np.asarray(faces)
+        par, wgt = synthetic.densify_table(self.smplx_model.V, faces, levels)
+        self._dense_par = torch.from_numpy(par).to(self._device)
+        self._dense_wgt = torch.from_numpy(wgt).to(self._device)
+
+    def fix_site_subset(self, seed: Optional[int] = None) -> torch.Tensor:
+        """Draw the densified-vertex subset once (the reference redraws ``torch.randperm`` on the global CPU
+        generator every forward, renderer.py:287); used for sequences that must keep the same sites."""
+        n = int(self._dense_par.shape[0])
+        g = None if seed is None else torch.Generator().manual_seed(seed)
+        self._fixed_idx = torch.randperm(n, generator=g)[:self.num_verts].to(self._device)
+        return self._fixed_idx
+
+    def get_smpl_vertices(self, smpl_params):
+        """renderer.py:245-290: posed vertices (no transl), optionally densified + subset -> [B*T, N, 3]."""
+        full, shape = self.smplx_model.full_pose(smpl_params)
+        verts = stages.lbs_forward(self.smplx_model, full, shape)
+        if getattr(self.cfg, "densify_smplx_verts", False):
+            idx = self._fixed_idx
+            if idx is None:
+                idx = torch.randperm(int(self._dense_par.shape[0]))[:self.num_verts].to(self._device)
+            verts = stages.densify_gather(verts, self._dense_par.index_select(0, idx).contiguous(),
+                                          self._dense_wgt.index_select(0, idx).contiguous())
+        return verts
+
+    def _decoder_wb(self):
+        return stages.decoder_matrix(self.gaussian_decoder)
+
+    def sample_from_triplane(self, triplane_features, points):
+        """renderer.py:292-317 ([F,3,C,Hp,Wp] or unbatched, points [F,N,3]) -> [F,N,3C] sampled features.
+        Kept for API compatibility (the forward pass never materialises this tensor): it is computed with the
+        projection kernel against an identity 'decoder', 6 channels at a time (slow; not the hot path)."""
+        batched = points.ndim == 3
+        if not batched:
+            triplane_features, points = triplane_features[None], points[None]
+        Fr, Np, C, Hp, Wp = triplane_features.shape
+        tokens = triplane_features.permute(0, 2, 1, 3, 4).reshape(Fr, C, Np * Hp * Wp).contiguous().float().to(self._device)
+        points = points.float().to(self._device)
+        N = points.shape[1]
+        out = torch.empty(Fr, N, Np * C, device=self._device)
+        zeros3 = torch.zeros(Fr, 3, device=self._device)
+        bias = torch.zeros(14, device=self._device)
+        rows = (0, 1, 2, 7, 8, 9)                    # heads that come back un-activated: xyz offset, scaling
+        for p in range(Np):
+            for c0 in range(0, C, 6):
+                n = min(6, C - c0)
+                W = torch.zeros(14, 3 + 3 * C, device=self._device)
+                for k in range(n):
+                    W[rows[k], 3 + p * C + c0 + k] = 1.0
+                proj = stages.triplane_project(tokens, W, C, Hp)
+                g = stages.sample_decode(proj, points, zeros3, W, bias, C, Hp, float(self.cfg.radius))
+                vals = torch.cat([g["xyz"] - points, g["scale"]], dim=-1)
+                out[:, :, p * C + c0:p * C + c0 + n] = vals[:, :, :n]
+        return out if batched else out.squeeze(0)
+
+    def construct_gaussians(self, gaussian_params, points, smpl_params):
+        """renderer.py:319-346 on already-decoded heads (API compatibility; forward() fuses this)."""
+        rot = torch.nn.functional.normalize(gaussian_params["rotation"], dim=-1)
+        color = torch.sigmoid(gaussian_params["shs"])
+        return {"xyz": points + gaussian_params["xyz_offset"] + smpl_params["transl"].reshape(-1, 1, 3),
+                "scale": gaussian_params["scaling"], "rot": rot, "opacity": gaussian_params["opacity"],
+                "color": color, "shs": color}
+
+    def decode_gaussians(self, triplane_features, points, transl):
+        """Stages 1+2 for [F,C,3*R*R] tokens and [F,N,3] posed sites -> the ``gaussians`` dict."""
+        C, R = int(self.cfg.triplane_feature_dim), int(self.cfg.triplane_resolution)
+        W, b = self._decoder_wb()
+        proj = stages.triplane_project(triplane_features, W, C, R)
+        return stages.sample_decode(proj, points, transl, W, b, C, R, float(self.cfg.radius))
+
+    def forward(self, triplane_features, cam_params, smpl_tokens=None, smpl_params_gt=None):
+        """renderer.py:73-204.  triplane_features [B,T,C,3*R*R]; cam_params {'intrinsic' [B,T,3,3], 'extrinsic'
+        [B,T,4,4]}; returns (rendered_images [B,T,H,W,3], gaussians[, pred_smpl_params])."""
+        dev = self._device
+        if smpl_tokens is not None:
+            B, T = smpl_tokens.shape[0], smpl_tokens.shape[1]
+        elif smpl_params_gt is not None:
+            B, T = triplane_features.shape[0], triplane_features.shape[1]
+        else:
+            raise ValueError("Renderer.forward needs smpl_tokens (with a smpl_decoder) or smpl_params_gt")
+        pred_smpl_params = None
+        if self.smpl_decoder is not None and smpl_tokens is not None:
+            pred_smpl_params = self.smpl_decoder(smpl_tokens.reshape(B * T, *smpl_tokens.shape[2:]))
+            for key in list(pred_smpl_params.keys()):           # renderer.py:111-118
+                v = pred_smpl_params[key]
+                if key in ("body_pose", "left_hand_pose", "right_hand_pose"):
+                    pred_smpl_params[key] = v.reshape(B, T, *v.shape[1:])
+                elif key in ("betas", "transl", "global_orient", "expression", "jaw_pose", "leye_pose", "reye_pose", "focal"):
+                    pred_smpl_params[key] = v.reshape(B, T, -1)
+        smpl_params = smpl_params_gt if smpl_params_gt is not None else pred_smpl_params
+        if smpl_params is None:
+            raise ValueError("no SMPL-X parameters: pass smpl_params_gt or build the Renderer with a smpl_decoder "
+                             "and cfg.predict_smplx_params=True")
+        C, R = int(self.cfg.triplane_feature_dim), int(self.cfg.triplane_resolution)
+        tokens = triplane_features.reshape(B * T, C, 3 * R * R)
+        if tokens.device != dev or tokens.dtype != torch.float32:
+            tokens = tokens.to(dev, torch.float32)
+        points = self.get_smpl_vertices(smpl_params)                                   # [F,N,3]
+        transl = smpl_params["transl"].reshape(B * T, 3).to(dev, torch.float32)
+        gaussians = self.decode_gaussians(tokens, points, transl)
+        rendered = render_batch(gaussians, cam_params["intrinsic"], cam_params["extrinsic"], self.cfg, debug=False)
+        if getattr(self.cfg, "predict_smplx_params", False):
+            return rendered, gaussians, pred_smpl_params
+        return rendered, gaussians

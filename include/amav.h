@@ -35,6 +35,8 @@ extern "C" {
 
 const char *amav_last_error(void);
 int amav_version(void);
+/* number of CUDA kernels this library has launched since it was loaded (all threads) */
+int64_t amav_launch_count(void);
 
 /* ---------------------------------------------------------------------------------------------
  * Stage 1: triplane projection.  Replaces the channel dimension of F.grid_sample + 5x nn.Linear
