@@ -31,7 +31,7 @@ _SIGS = {
     "amav_splat_preprocess": [ctypes.POINTER(SplatDims)] + [c_void_p] * 12 + [c_void_p],
     "amav_splat_scan": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_void_p],
     "amav_splat_bin": [ctypes.POINTER(SplatDims)] + [c_void_p] * 6 + [c_int64, c_void_p, c_void_p],
-    "amav_splat_blend": [ctypes.POINTER(SplatDims)] + [c_void_p] * 4 + [c_int, c_int] + [c_void_p] * 4 + [c_void_p],
+    "amav_splat_blend": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_int64, c_void_p, c_int, c_int] + [c_void_p] * 5 + [c_void_p],
 }
 
 _lib = None

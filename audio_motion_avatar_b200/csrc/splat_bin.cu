@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(256) scatter_entries(int64_t total, int N, int
     if (rc.z <= rc.x || rc.w <= rc.y) return;
     const int f = (int)(gid / N);
     const uint32_t i = (uint32_t)(gid - (int64_t)f * N);
-    const float depth = geom[3 * gid + 2].y;
+    const float depth = geom[3 * gid + 2].z;
     const uint64_t e = ((uint64_t)__float_as_uint(depth) << 32) | (uint64_t)i;
     const int64_t tbase = (int64_t)f * tiles;
     for (int y = rc.y; y < rc.w; ++y)

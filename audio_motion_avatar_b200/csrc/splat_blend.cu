@@ -46,29 +46,39 @@ struct BlendParams {
     float *out_color, *final_T, *out_invdepth;
     int32_t *n_contrib;
     unsigned int *work_counter;
+    uint32_t capacity;
 };
 
 constexpr int BLEND_THREADS = 256;
 
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams p, const float *__restrict__ bg)
 {
-    __shared__ float4 s_g0[BLEND_THREADS];
-    __shared__ float4 s_g1[BLEND_THREADS];
-    __shared__ float2 s_g2[BLEND_THREADS];
+    __shared__ float4 s_g0[BLEND_THREADS];     // x, y, -conic.x/2, -conic.y
+    __shared__ float4 s_g1[BLEND_THREADS];     // -conic.z/2, opacity, pmin, r
+    __shared__ float4 s_g2[BLEND_THREADS];     // g, b, depth, radius
+    __shared__ unsigned int s_next;
     const int tiles = p.gx * p.gy;
-    const int64_t total_tiles = (int64_t)p.F * tiles;
+    const unsigned int total_tiles = (unsigned int)((int64_t)p.F * tiles);
     const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
     const int lx = threadIdx.x & 15, ly = threadIdx.x >> 4;
     const float alpha_min = 1.0f / 255.0f;
 
-    for (int64_t t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (;;) {
+        // tiles differ in depth by orders of magnitude (the body covers ~20% of the image): CTAs pull the next
+        // tile from a device counter instead of striding, so no SM idles behind a column of deep tiles
+        if (threadIdx.x == 0) s_next = atomicAdd(p.work_counter, 1u);
+        __syncthreads();
+        const unsigned int t = s_next;
+        if (t >= total_tiles) break;
         const int f = (int)(t / tiles);
-        const int tile = (int)(t - (int64_t)f * tiles);
+        const int tile = (int)(t - (unsigned int)f * tiles);
         const int ty = tile / p.gx, tx = tile - ty * p.gx;
         const int pxi = tx * 16 + lx, pyi = ty * 16 + ly;
         const bool inside = pxi < p.W && pyi < p.H;
         const float pxf = (float)pxi, pyf = (float)pyi;
-        const uint32_t r0 = p.tile_start[t], r1 = p.tile_start[t + 1];
+        // ranges are clamped to the caller's entry capacity: after a bucket overflow the frame is incomplete (the
+        // overflow flag tells the host) but nothing is read out of bounds
+        const uint32_t r0 = min(p.tile_start[t], p.capacity), r1 = min(p.tile_start[t + 1], p.capacity);
         const float4 *geom = p.geom + (int64_t)f * p.N * 3;
 
         float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dv = 0.0f;
@@ -79,32 +89,35 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             if (__syncthreads_count(done) == BLEND_THREADS) break;
             if (base + threadIdx.x < r1) {
                 const int g = p.point_list[base + threadIdx.x];
-                const float4 a = geom[3 * (int64_t)g], b = geom[3 * (int64_t)g + 1], c = geom[3 * (int64_t)g + 2];
-                s_g0[threadIdx.x] = a;
-                s_g1[threadIdx.x] = b;
-                s_g2[threadIdx.x] = make_float2(c.x, c.y);
+                const float4 *src = geom + 3 * (int64_t)g;
+                s_g0[threadIdx.x] = src[0];
+                s_g1[threadIdx.x] = src[1];
+                s_g2[threadIdx.x] = src[2];
             }
             __syncthreads();
             const int nb = todo < BLEND_THREADS ? todo : BLEND_THREADS;
-            for (int j = 0; !done && j < nb; ++j) {
-                ++contributor;
-                const float4 a = s_g0[j];
-                const float dx = a.x - pxf, dy = a.y - pyf;
-                const float4 b = s_g1[j];
-                const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (b.x * dy) * dy);
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, b.y * amav_exp(power));
-                if (alpha < alpha_min) continue;
-                const float Tn = T * (1.0f - alpha);
-                if (Tn < 0.0001f) { done = true; continue; }
-                const float w = alpha * T;
-                const float2 c = s_g2[j];
-                C0 = fmaf(b.z, w, C0);
-                C1 = fmaf(b.w, w, C1);
-                C2 = fmaf(c.x, w, C2);
-                if (p.out_invdepth) Dv = fmaf(1.0f / c.y, w, Dv);
-                T = Tn;
-                last = contributor;
+            if (!done) {
+                for (int j = 0; j < nb; ++j) {
+                    const float4 a = s_g0[j];
+                    const float4 b = s_g1[j];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (b.x * dy) * dy);
+                    if (power > 0.0f || power < b.z) continue;          // b.z = pmin: alpha surely < 1/255
+                    const float alpha = fminf(0.99f, b.y * amav_exp(power));
+                    if (alpha < alpha_min) continue;
+                    const float Tn = T * (1.0f - alpha);
+                    if (Tn < 0.0001f) { done = true; contributor += j + 1; goto batch_done; }
+                    const float w = alpha * T;
+                    const float4 c = s_g2[j];
+                    C0 = fmaf(b.w, w, C0);
+                    C1 = fmaf(c.x, w, C1);
+                    C2 = fmaf(c.y, w, C2);
+                    if (p.out_invdepth) Dv = fmaf(1.0f / c.z, w, Dv);
+                    T = Tn;
+                    last = contributor + j + 1;
+                }
+                contributor += nb;
+            batch_done:;
             }
         }
         if (inside) {
@@ -134,19 +147,22 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
 }  // namespace
 
 extern "C" int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
-                                const int32_t *point_list, const float *bg, int hwc, int clamp01,
+                                const int32_t *point_list, int64_t capacity, const float *bg, int hwc, int clamp01,
                                 float *out_color, float *final_T, int32_t *n_contrib, float *out_invdepth,
-                                void *stream)
+                                uint32_t *work_counter, void *stream)
 {
     AMAV_CHECK_ARG(d && d->frames >= 0 && d->width > 0 && d->height > 0, "bad dims");
     if (d->frames == 0) return AMAV_OK;
-    AMAV_CHECK_ARG(tile_start && bg && out_color, "null buffer");
+    AMAV_CHECK_ARG(tile_start && bg && out_color && work_counter, "null buffer");
+    AMAV_CHECK_ARG((int64_t)d->frames * ((d->width + 15) / 16) * ((d->height + 15) / 16) < ((int64_t)1 << 31), "too many tiles");
     BlendParams p;
     p.F = d->frames; p.N = d->num_gaussians; p.W = d->width; p.H = d->height;
     p.gx = (d->width + 15) / 16; p.gy = (d->height + 15) / 16; p.hwc = hwc; p.clamp01 = clamp01;
     p.geom = reinterpret_cast<const float4 *>(geom); p.tile_start = tile_start; p.point_list = point_list;
     p.out_color = out_color; p.final_T = final_T; p.n_contrib = n_contrib; p.out_invdepth = out_invdepth;
-    p.work_counter = nullptr; p.bg0 = p.bg1 = p.bg2 = 0.f;
+    p.work_counter = work_counter;
+    AMAV_CHECK_ARG(capacity >= 0, "bad capacity");
+    p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity; p.bg0 = p.bg1 = p.bg2 = 0.f;
     const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;
     const int grid = (int)(total_tiles < AMAV_SM_COUNT * 8 ? total_tiles : AMAV_SM_COUNT * 8);
     blend_kernel<<<grid, BLEND_THREADS, 0, (cudaStream_t)stream>>>(p, bg);

@@ -139,9 +139,13 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessParams 
                 const int maxy = min(p.gy, max(0, (int)((piy + (float)rad + 15.0f) / 16.0f)));
                 touched = (maxx - minx) * (maxy - miny);
                 if (touched > 0) {
+                    // blend skips a pair before evaluating exp() when power < pmin: alpha = op*exp(power) is then
+                    // below 1/255 with a 1e-4 relative margin, far above the rounding of logf/exp, so the exact
+                    // alpha < 1/255 test that follows sees every borderline pair (bit-exact lists are kept).
+                    const float pmin = logf((1.0f / 255.0f) / op) - 1.0e-4f;
                     g0 = make_float4(pix, piy, -0.5f * conx, -cony);
-                    g1 = make_float4(-0.5f * conz, op, cr, cg);
-                    g2 = make_float4(cb, pvz, (float)rad, 0.0f);
+                    g1 = make_float4(-0.5f * conz, op, pmin, cr);
+                    g2 = make_float4(cg, cb, pvz, (float)rad);
                     rc = make_ushort4((unsigned short)minx, (unsigned short)miny, (unsigned short)maxx,
                                       (unsigned short)maxy);
                     uint32_t *cnt = p.tile_count + (int64_t)f * p.gx * p.gy;

@@ -92,9 +92,15 @@ def _workspace(device) -> SplatWorkspace:
     return ws
 
 
-def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug, views_per_set, hwc):
+def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug, views_per_set, hwc,
+                   out=None, defer_check=False):
     """All frames of a call in one batched splat pass.  Gaussian tensors [G,N,k] (pre-activation scale and
-    opacity as in the reference's ``gaussians`` dict), cameras [G*views_per_set,...]."""
+    opacity as in the reference's ``gaussians`` dict), cameras [G*views_per_set,...].
+
+    Host syncs: the first call on a device reads the entry count D back once to size the bucket buffer; later
+    calls trust the cached capacity (grown by 25%) and only read the overflow flag AFTER everything is enqueued
+    (``defer_check`` leaves even that to the caller, see ``Renderer.render_sequence``).  An overflow re-renders
+    with the sizing read."""
     if not getattr(args, "rgb", True):
         # renderer.py:541-545 feeds 3-channel colours to eval_sh(sh_degree=3), which asserts on the coefficient
         # count (graphic_utils.py:722): the branch is dead in the reference too.
@@ -112,10 +118,18 @@ def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug,
         opacity = torch.full_like(opacity, 0.1)
         color = color.clamp(0.0, 1.0)
         activate = False
-    out = splat_forward(xyz, scale, rot, opacity, color, view, full, tanfov, bg, height, width,
-                        views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=True,
-                        workspace=_workspace(dev))
-    return out["color"]
+    ws = _workspace(dev)
+
+    def run(sync_free):
+        return splat_forward(xyz, scale, rot, opacity, color, view, full, tanfov, bg, height, width,
+                             views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=True,
+                             workspace=ws, sync_free=sync_free, out=out)
+
+    res = run(sync_free=ws.capacity > 0)
+    if res["D"] < 0 and not defer_check:
+        if int(ws.overflow.item()) != 0:
+            res = run(sync_free=False)
+    return res["color"]
 
 
 def render_batch(gaussians, K, E, args, bg_color=None, debug=False):
@@ -347,3 +361,96 @@ class Renderer(nn.Module):
         if getattr(self.cfg, "predict_smplx_params", False):
             return rendered, gaussians, pred_smpl_params
         return rendered, gaussians
+
+    # -- host-resident sequences ------------------------------------------------------------------
+    def render_sequence(self, triplane_features, cam_params, smpl_params, chunk: int = 8, out=None):
+        """Render a [B,T] frame sequence whose triplane tokens live in (pinned) HOST memory and return the
+        frames in pinned host memory: the stage-2 demo loop of the reference (main2.py:179-239) hands the
+        renderer one clip after another and copies every frame back for the video sink.
+
+        Frames are independent, so the sequence is cut into ``chunk``-frame pieces that flow through three
+        streams: host->device copy of chunk k+1, render of chunk k, device->host copy of chunk k-1.
+        LBS for the whole sequence runs once up front (its inputs are a few KB per frame)."""
+        dev = self._device
+        B, T = triplane_features.shape[0], triplane_features.shape[1]
+        Fr = B * T
+        C, R = int(self.cfg.triplane_feature_dim), int(self.cfg.triplane_resolution)
+        H, W = int(self.cfg.image_size[0]), int(self.cfg.image_size[1])
+        tok = triplane_features.reshape(Fr, C, 3 * R * R)
+        if tok.dtype != torch.float32:
+            raise ValueError("triplane_features must be fp32")
+        if out is None:
+            out = torch.empty(B, T, H, W, 3, dtype=torch.float32, pin_memory=True)
+        out_f = out.reshape(Fr, H, W, 3)
+        main = torch.cuda.current_stream(dev)
+        params = {k: v.to(dev, non_blocking=True) for k, v in smpl_params.items()}
+        K = cam_params["intrinsic"].reshape(Fr, 3, 3).to(dev, non_blocking=True)
+        E = cam_params["extrinsic"].reshape(Fr, 4, 4).to(dev, non_blocking=True)
+        points = self.get_smpl_vertices(params)
+        transl = params["transl"].reshape(Fr, 3).float()
+        Wd, bd = self._decoder_wb()
+        Wd, bd = Wd.detach().contiguous(), bd.detach().contiguous()
+        st = self._seq_state(chunk, C, R, H, W)
+        h2d, d2h = st["h2d"], st["d2h"]
+        h2d.wait_stream(main)
+        nchunks = (Fr + chunk - 1) // chunk
+        pending = []
+        for k in range(nchunks):
+            f0, f1 = k * chunk, min(Fr, (k + 1) * chunk)
+            n = f1 - f0
+            slot = k % st["depth"]
+            with torch.cuda.stream(h2d):
+                if st["tok_free"][slot] is not None:
+                    h2d.wait_event(st["tok_free"][slot])           # render of chunk k-depth has consumed the buffer
+                st["tok"][slot][:n].copy_(tok[f0:f1], non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(h2d)
+            main.wait_event(ready)
+            if st["img_free"][slot] is not None:
+                main.wait_event(st["img_free"][slot])              # D2H of chunk k-depth has drained the image buffer
+            proj = stages.triplane_project(st["tok"][slot][:n], Wd, C, R, out=st["proj"][:n])
+            consumed = torch.cuda.Event()
+            consumed.record(main)
+            st["tok_free"][slot] = consumed
+            g = stages.sample_decode(proj, points[f0:f1], transl[f0:f1], Wd, bd, C, R, float(self.cfg.radius))
+            img = st["img"][slot][:n]
+            _render_frames(g["xyz"], g["rot"], g["scale"], g["opacity"], g["color"], K[f0:f1], E[f0:f1], self.cfg,
+                           None, False, 1, True, out=img, defer_check=True)
+            ws = _workspace(dev)
+            pending.append((k, ws.overflow.clone() if ws.overflow is not None else None))
+            rendered = torch.cuda.Event()
+            rendered.record(main)
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(rendered)
+                out_f[f0:f1].copy_(img, non_blocking=True)
+                drained = torch.cuda.Event()
+                drained.record(d2h)
+            st["img_free"][slot] = drained
+        main.wait_stream(d2h)
+        main.synchronize()
+        bad = [k for k, flag in pending if flag is not None and int(flag.item()) != 0]
+        for k in bad:                                              # bucket overflow: redo the chunk with the sizing read
+            f0, f1 = k * chunk, min(Fr, (k + 1) * chunk)
+            tk = tok[f0:f1].to(dev)
+            g = self.decode_gaussians(tk, points[f0:f1], transl[f0:f1])
+            _workspace(dev).capacity = 0
+            img = _render_frames(g["xyz"], g["rot"], g["scale"], g["opacity"], g["color"], K[f0:f1], E[f0:f1], self.cfg,
+                                 None, False, 1, True)
+            out_f[f0:f1].copy_(img)
+        return out
+
+    def _seq_state(self, chunk, C, R, H, W, depth: int = 3):
+        key = (chunk, C, R, H, W, depth)
+        st = getattr(self, "_seq", None)
+        if st is None or st["key"] != key:
+            dev = self._device
+            st = {"key": key, "depth": depth, "h2d": torch.cuda.Stream(dev), "d2h": torch.cuda.Stream(dev),
+                  "tok": [torch.empty(chunk, C, 3 * R * R, device=dev) for _ in range(depth)],
+                  "img": [torch.empty(chunk, H, W, 3, device=dev) for _ in range(depth)],
+                  "proj": torch.empty(chunk, 3, R * R, 16, device=dev),
+                  "tok_free": [None] * depth, "img_free": [None] * depth}
+            self._seq = st
+        else:
+            st["tok_free"] = [None] * st["depth"]
+            st["img_free"] = [None] * st["depth"]
+        return st

@@ -90,8 +90,9 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     geom = ws.get("geom", F * N * 12, torch.float32, dev)
     rect = ws.get("rect", F * N * 4, torch.int16, dev)
     touched = ws.get("tiles_touched", F * N, torch.int32, dev)
-    counters = ws.get("counters", 2 * nt + 1, torch.int32, dev, zero=True)     # tile_count | tile_cursor | overflow
+    counters = ws.get("counters", 2 * nt + 2, torch.int32, dev, zero=True)     # tile_count | tile_cursor | overflow | work
     tile_count, tile_cursor, overflow = counters[:nt], counters[nt:2 * nt], counters[2 * nt:2 * nt + 1]
+    work_counter = counters[2 * nt + 1:2 * nt + 2]
     tile_start = ws.get("tile_start", nt + 1, torch.int32, dev)
     scan_tmp = ws.get("scan_tmp", int(_lib.lib().amav_splat_scan_tmp_elems(nt)), torch.int32, dev)
     ws.overflow = overflow
@@ -116,8 +117,8 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     final_T = torch.empty(F, height, width, dtype=torch.float32, device=dev) if want_aux else None
     n_contrib = torch.empty(F, height, width, dtype=torch.int32, device=dev) if want_aux else None
     invdepth = torch.empty(F, 1, height, width, dtype=torch.float32, device=dev) if want_invdepth else None
-    call("amav_splat_blend", dims, ptr(geom), ptr(tile_start), ptr(ws.point_list), ptr(bg), int(hwc), int(clamp01),
-         ptr(out), ptr(final_T), ptr(n_contrib), ptr(invdepth), st)
+    call("amav_splat_blend", dims, ptr(geom), ptr(tile_start), ptr(ws.point_list), ws.capacity, ptr(bg), int(hwc), int(clamp01),
+         ptr(out), ptr(final_T), ptr(n_contrib), ptr(invdepth), ptr(work_counter), st)
     return {"color": out, "geom": geom.view(F, N, 12), "rect": rect.view(F, N, 4), "tiles_touched": touched.view(F, N),
             "tile_start": tile_start, "point_list": ws.point_list, "D": D, "final_T": final_T,
             "n_contrib": n_contrib, "invdepth": invdepth, "workspace": ws}

@@ -107,7 +107,8 @@ typedef struct AmavSplatDims {
 
 /* 4a  per-Gaussian projection (upstream preprocessCUDA) + per-tile counting.
  *   view, proj [F,16]; tanfov [F,2] = (tanfovx, tanfovy)
- *   geom   [F,N,12] fp32: (x, y, -conic.x/2, -conic.y) (-conic.z/2, opacity, r, g) (b, depth, radius, 0)
+ *   geom   [F,N,12] fp32: (x, y, -conic.x/2, -conic.y) (-conic.z/2, opacity, pmin, r) (g, b, depth, radius);
+ *          pmin = log((1/255)/opacity) - 1e-4: blend's conservative pre-test before exp()
  *   rect   [F,N,4] uint16: tile rectangle (minx, miny, maxx, maxy); all zero when culled
  *   tiles_touched [F,N] int32
  *   tile_count [F*tiles] uint32: MUST be zeroed by the caller; incremented once per (Gaussian, tile)
@@ -141,11 +142,13 @@ int amav_splat_bin(const AmavSplatDims *d, const float *geom, const uint16_t *re
  *   bg [3]; out_color [F,3,H,W] (hwc=0) or [F,H,W,3] (hwc=1, the layout render_batch returns,
  *   renderer.py:477-479); clamp01=1 applies renderer.py:568.
  *   final_T [F,H,W], n_contrib [F,H,W] int32, out_invdepth [F,H,W]: each may be NULL (inference).
+ *   capacity: entries in point_list (same value as given to amav_splat_bin); tile ranges are clamped to it.
+ *   work_counter [1] uint32: MUST be zeroed by the caller (tiles are handed to CTAs dynamically).
  */
 int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
-                     const int32_t *point_list, const float *bg, int hwc, int clamp01,
+                     const int32_t *point_list, int64_t capacity, const float *bg, int hwc, int clamp01,
                      float *out_color, float *final_T, int32_t *n_contrib, float *out_invdepth,
-                     void *stream);
+                     uint32_t *work_counter, void *stream);
 
 #ifdef __cplusplus
 }

@@ -311,3 +311,38 @@ def render_one(g_frame: Dict[str, torch.Tensor], K: torch.Tensor, E: torch.Tenso
     scales, opac, col = activate_for_raster(g_frame)
     _, _, out = rasterize(g_frame["xyz"], scales, g_frame["rot"], opac, col, view, full, tfx, tfy, bg, width, height)
     return torch.from_numpy(out["color"]).clamp(0, 1)
+
+
+# ----------------------------------------------------------------------------------------
+# the reference's own op sequence for query + decode, for the timed CPU baseline
+# ----------------------------------------------------------------------------------------
+def sample_from_triplane_torch(triplane: torch.Tensor, points: torch.Tensor, radius: float) -> torch.Tensor:
+    """renderer.py:292-317 with the reference's own PyTorch calls (F.grid_sample on [(F*3),C,Hp,Wp], then the
+    '(B Np) Cp () N -> B N (Np Cp)' transpose), used where the CPU baseline must cost what the reference costs.
+    Checked against ``sample_from_triplane`` (the explicit restatement) in tests/test_oracle_golden.py."""
+    Fr, Np, Cc, Hp, Wp = triplane.shape
+    pos = torch.clamp(points / radius, -1, 1)
+    idx = torch.stack((pos[..., [0, 1]], pos[..., [0, 2]], pos[..., [1, 2]]), dim=-3)           # [F,3,N,2]
+    out = torch.nn.functional.grid_sample(triplane.reshape(Fr * Np, Cc, Hp, Wp), idx.reshape(Fr * Np, 1, -1, 2),
+                                          align_corners=False, mode="bilinear")                # [(F 3),C,1,N]
+    return out.reshape(Fr, Np, Cc, -1).permute(0, 3, 1, 2).reshape(Fr, -1, Np * Cc)
+
+
+def reference_frames(model, weights, tokens, params, K, E, height, width, channels, res, radius=1.4,
+                     level_edges=None, site_idx=None, bg=(1.0, 1.0, 1.0)):
+    """The reference's Renderer.forward (renderer.py:73-204) for F frames on the CPU: LBS -> (subdivide + subset)
+    -> grid_sample twice (the reference samples at initial and refined points, renderer.py:136,158; the refiner
+    offset is exactly zero at init) -> five Linear heads -> construct_gaussians -> per-frame render_one.
+    tokens [F,C,3*R*R]; params flattened to [F,...].  Returns images [F,H,W,3]."""
+    pts = lbs_vertices(params, model)
+    if level_edges is not None:
+        pts = subdivide_vertices(pts, level_edges)
+    if site_idx is not None:
+        pts = pts[:, site_idx]
+    Fr = tokens.shape[0]
+    tri = tokens.reshape(Fr, channels, 3, res, res).permute(0, 2, 1, 3, 4)
+    sample_from_triplane_torch(tri, pts, radius)                                               # renderer.py:136
+    feats = sample_from_triplane_torch(tri, pts, radius)                                       # renderer.py:158
+    g = construct_gaussians(decode_heads(pts, feats, weights), pts, params["transl"])
+    imgs = [render_one({k: v[f] for k, v in g.items()}, K[f], E[f], height, width, bg).permute(1, 2, 0) for f in range(Fr)]
+    return torch.stack(imgs), g

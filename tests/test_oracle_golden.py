@@ -52,3 +52,11 @@ def test_activation_matches_reference(golden_dir):
     assert np.array_equal(s.numpy(), g["scales"])
     assert np.array_equal(o.numpy(), g["opac"])
     assert np.array_equal(c.numpy(), g["col"])
+
+
+def test_grid_sample_baseline_equals_explicit_restatement(golden_dir):
+    g = _load(golden_dir, "ref_query_decode.npz")
+    tri, pts = torch.from_numpy(g["triplane"]), torch.from_numpy(g["points"])
+    a = O.sample_from_triplane_torch(tri, pts, float(g["radius"]))
+    assert (a - torch.from_numpy(g["feats"])).abs().max().item() <= 1e-6
+    assert (a - O.sample_from_triplane(tri, pts, float(g["radius"]))).abs().max().item() <= 2e-6

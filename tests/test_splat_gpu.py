@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 import torch
 
-from tests.helpers import oracle_frames, random_scene, psnr
+from tests.helpers import oracle_cameras, oracle_frames, random_scene, psnr
 
 pytestmark = pytest.mark.gpu
 
@@ -26,8 +26,8 @@ def _check_frame(out, f, pre, binned, img, N, H, W):
     live = pre["radii"] > 0
     assert np.array_equal(out["tiles_touched"][f].cpu().numpy(), pre["tiles_touched"])
     assert np.array_equal(out["rect"][f].cpu().numpy().astype(np.int32)[live], pre["rect"][live])
-    assert np.array_equal(geom[live, 9].view(np.uint32), pre["depth"][live].view(np.uint32))       # depth bits
-    assert np.array_equal(geom[live, 10].astype(np.int32), pre["radii"][live])
+    assert np.array_equal(geom[live, 10].view(np.uint32), pre["depth"][live].view(np.uint32))       # depth bits
+    assert np.array_equal(geom[live, 11].astype(np.int32), pre["radii"][live])
     assert np.array_equal(geom[live, 0:2].view(np.uint32), pre["xy"][live].view(np.uint32))
     con = pre["conic_opacity"][live]
     assert np.array_equal(geom[live, 2], -0.5 * con[:, 0]) and np.array_equal(geom[live, 3], -con[:, 1])
@@ -43,7 +43,7 @@ def _check_frame(out, f, pre, binned, img, N, H, W):
     assert np.array_equal(pl, binned["point_list"])                                                # sort order
     # upstream keys rebuilt from (tile, depth bits of the listed Gaussian)
     tile_of = np.repeat(np.arange(tiles, dtype=np.uint64), cnt)
-    keys = (tile_of << np.uint64(32)) | geom[pl, 9].view(np.uint32).astype(np.uint64)
+    keys = (tile_of << np.uint64(32)) | geom[pl, 10].view(np.uint32).astype(np.uint64)
     assert np.array_equal(keys, binned["keys"])
     assert np.array_equal(out["n_contrib"][f].cpu().numpy(), img["n_contrib"])
     assert np.array_equal(out["final_T"][f].cpu().numpy(), img["final_T"])
@@ -105,3 +105,44 @@ def test_hwc_clamp_layout_and_activation():
     _, _, _, outs2 = oracle_frames(sc2, H, W)
     c = _run_cuda(raw, view, full, tan, H, W, (1.0, 1.0, 1.0), activate=True)["color"][0].cpu().numpy()
     assert np.abs(c - outs2[0][2]["color"]).max() <= 1e-3 and psnr(c, outs2[0][2]["color"]) >= 60.0
+
+
+def test_bucket_overflow_is_flagged_not_fatal_and_renderer_recovers():
+    """sync_free mode trusts the cached entry capacity; a scene that needs more sets the overflow flag, reads nothing
+    out of bounds, and render_batch re-renders with the sizing read."""
+    from types import SimpleNamespace
+    from audio_motion_avatar_b200.splat import SplatWorkspace, splat_forward
+    from audio_motion_avatar_b200 import renderer as Rn
+    d = torch.device("cuda:0")
+    H, W = 128, 128
+    small, big = random_scene(200, W, H, seed=1), random_scene(20000, W, H, seed=2)
+    ws = SplatWorkspace()
+
+    def run(sc, **kw):
+        view, full, tan = oracle_cameras(sc, H, W)
+        c = lambda t: t.to(d)
+        return splat_forward(c(sc["means"])[None], c(sc["scales"])[None], c(sc["rots"])[None], c(sc["opac"])[None],
+                             c(sc["col"])[None], c(view), c(full), c(tan), torch.ones(3, device=d), H, W, workspace=ws, **kw)
+
+    run(small)
+    cap = ws.capacity
+    out = run(big, sync_free=True)
+    torch.cuda.synchronize()
+    assert out["D"] == -1 and ws.capacity == cap and int(ws.overflow.item()) == 1
+    with pytest.raises(Exception):
+        ws.check()
+    ref = run(big)["color"].clone()
+    # through the public API: first a small call to seed the per-device workspace, then the big one
+    args = SimpleNamespace(image_size=(H, W), rgb=True, sh_degree=3)
+    Rn._WORKSPACES.clear()
+
+    def gs(sc):
+        return {"xyz": sc["means"][None].to(d), "rot": sc["rots"][None].to(d), "scale": (torch.log(sc["scales"]) + 3.9)[None].to(d),
+                "opacity": torch.logit(sc["opac"].clamp(1e-4, 1 - 1e-4))[None].to(d), "color": sc["col"][None].to(d)}
+
+    K, E = small["K"][None].to(d), small["E"][None].to(d)
+    Rn.render_batch(gs(small), K, E, args)
+    a = Rn.render_batch(gs(big), K, E, args)
+    Rn._WORKSPACES.clear()
+    b = Rn.render_batch(gs(big), K, E, args)
+    assert torch.equal(a, b)
