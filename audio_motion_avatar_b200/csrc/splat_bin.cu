@@ -128,25 +128,27 @@ __global__ void __launch_bounds__(256) scatter_entries(int64_t total, int N, int
         }
 }
 
-// Ascending bitonic sort of n entries (virtual +inf padding to P = next pow2): every
-// compare-exchange moves the minimum to the lower index, so pairs with hi >= n are no-ops.
+// Ascending bitonic sort of n entries (virtual +inf padding to P = 2^logP): every compare-exchange moves the
+// minimum to the lower index, so pairs with hi >= n are no-ops.  All index math is shifts and masks.
 template <typename Ptr>
-__device__ __forceinline__ void bitonic_sort(Ptr a, int n, int P)
+__device__ __forceinline__ void bitonic_sort(Ptr a, int n, int logP)
 {
-    for (int k = 2; k <= P; k <<= 1) {
-        const int hk = k >> 1;
-        for (int i = threadIdx.x; i < (P >> 1); i += blockDim.x) {        // flip step
-            const int blk = i / hk, r = i - blk * hk;
-            const int lo = blk * k + r, hi = blk * k + k - 1 - r;
+    const int half = 1 << (logP - 1);
+    for (int lk = 1; lk <= logP; ++lk) {                 // merge size k = 2^lk
+        const int lhk = lk - 1, hk = 1 << lhk;
+        for (int i = threadIdx.x; i < half; i += blockDim.x) {            // flip step
+            const int blk = i >> lhk, r = i & (hk - 1);
+            const int lo = (blk << lk) + r, hi = (blk << lk) + (2 * hk - 1) - r;
             if (hi < n) {
                 const uint64_t x = a[lo], y = a[hi];
                 if (y < x) { a[lo] = y; a[hi] = x; }
             }
         }
         __syncthreads();
-        for (int j = hk >> 1; j >= 1; j >>= 1) {
-            for (int i = threadIdx.x; i < (P >> 1); i += blockDim.x) {
-                const int lo = ((i / j) * (j << 1)) + (i % j), hi = lo + j;
+        for (int lj = lhk - 1; lj >= 0; --lj) {          // half-cleaners, stride j = 2^lj
+            const int j = 1 << lj;
+            for (int i = threadIdx.x; i < half; i += blockDim.x) {
+                const int lo = ((i >> lj) << (lj + 1)) + (i & (j - 1)), hi = lo + j;
                 if (hi < n) {
                     const uint64_t x = a[lo], y = a[hi];
                     if (y < x) { a[lo] = y; a[hi] = x; }
@@ -158,15 +160,23 @@ __device__ __forceinline__ void bitonic_sort(Ptr a, int n, int P)
 }
 
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_CAP = 8192;     // entries sorted in shared memory (64 KB); larger buckets sort in place in L2/HBM
+constexpr int SORT_CAP = 4096;     // entries sorted in shared memory (32 KB); larger buckets sort in place in L2/HBM
 
-__global__ void __launch_bounds__(SORT_THREADS) sort_tiles(int64_t num_tiles_total,
+// CTAs pull tiles from a device counter (bucket sizes range from 0 to thousands of entries).
+__global__ void __launch_bounds__(SORT_THREADS) sort_tiles(unsigned int num_tiles_total,
                                                             const uint32_t *__restrict__ tile_start,
                                                             uint64_t *__restrict__ entries,
-                                                            int32_t *__restrict__ point_list, int64_t capacity)
+                                                            int32_t *__restrict__ point_list, int64_t capacity,
+                                                            unsigned int *work_counter)
 {
-    extern __shared__ uint64_t s_ent[];
-    for (int64_t t = blockIdx.x; t < num_tiles_total; t += gridDim.x) {
+    __shared__ uint64_t s_ent[SORT_CAP];
+    __shared__ unsigned int s_next;
+    for (;;) {
+        if (threadIdx.x == 0) s_next = atomicAdd(work_counter, 1u);
+        __syncthreads();
+        const unsigned int t = s_next;
+        __syncthreads();
+        if (t >= num_tiles_total) break;
         const int64_t s = tile_start[t];
         int64_t e = tile_start[t + 1];
         if (e > capacity) e = capacity;
@@ -176,20 +186,17 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_tiles(int64_t num_tiles_tot
             if (threadIdx.x == 0) point_list[s] = (int32_t)(uint32_t)entries[s];
             continue;
         }
-        int P = 2;
-        while (P < n) P <<= 1;
+        int logP = 1;
+        while ((1 << logP) < n) ++logP;
         if (n <= SORT_CAP) {
             for (int i = threadIdx.x; i < n; i += blockDim.x) s_ent[i] = entries[s + i];
             __syncthreads();
-            bitonic_sort(s_ent, n, P);
+            bitonic_sort(s_ent, n, logP);
             for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
-            __syncthreads();
         } else {
             uint64_t *g = entries + s;
-            __syncthreads();
-            bitonic_sort(g, n, P);
+            bitonic_sort(g, n, logP);
             for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)g[i];
-            __syncthreads();
         }
     }
 }
@@ -226,6 +233,7 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
 {
     AMAV_CHECK_ARG(d && d->frames >= 0 && d->num_gaussians >= 0, "bad dims");
     AMAV_CHECK_ARG(tile_start && tile_cursor && overflow, "null buffer");
+    AMAV_CHECK_ARG((int64_t)d->frames * ((d->width + 15) / 16) * ((d->height + 15) / 16) < ((int64_t)1 << 31), "too many tiles");
     AMAV_CHECK_ARG(capacity >= 0 && (capacity == 0 || (entries && point_list)), "null entries");
     cudaStream_t stream = (cudaStream_t)stream_;
     const int gx = (d->width + 15) / 16, gy = (d->height + 15) / 16;
@@ -238,13 +246,9 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
         total, d->num_gaussians, gx, tiles, reinterpret_cast<const float4 *>(geom),
         reinterpret_cast<const ushort4 *>(rect), tile_start, tile_cursor, entries, capacity, overflow);
     AMAV_CHECK_LAUNCH();
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_CAP * 8);
-        attr_set = true;
-    }
-    const int grid = (int)(nt < AMAV_SM_COUNT * 3 ? nt : AMAV_SM_COUNT * 3);
-    sort_tiles<<<grid, SORT_THREADS, SORT_CAP * 8, stream>>>(nt, tile_start, entries, point_list, capacity);
+    const int grid = (int)(nt < AMAV_SM_COUNT * 6 ? nt : AMAV_SM_COUNT * 6);
+    sort_tiles<<<grid, SORT_THREADS, 0, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
+                                                  reinterpret_cast<unsigned int *>(overflow) + 1);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }

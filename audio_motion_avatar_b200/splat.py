@@ -90,12 +90,12 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     geom = ws.get("geom", F * N * 12, torch.float32, dev)
     rect = ws.get("rect", F * N * 4, torch.int16, dev)
     touched = ws.get("tiles_touched", F * N, torch.int32, dev)
-    counters = ws.get("counters", 2 * nt + 2, torch.int32, dev, zero=True)     # tile_count | tile_cursor | overflow | work
-    tile_count, tile_cursor, overflow = counters[:nt], counters[nt:2 * nt], counters[2 * nt:2 * nt + 1]
-    work_counter = counters[2 * nt + 1:2 * nt + 2]
+    counters = ws.get("counters", 2 * nt + 3, torch.int32, dev, zero=True)  # tile_count | tile_cursor | overflow, sort queue | blend queue
+    tile_count, tile_cursor, overflow = counters[:nt], counters[nt:2 * nt], counters[2 * nt:2 * nt + 2]
+    work_counter = counters[2 * nt + 2:2 * nt + 3]
     tile_start = ws.get("tile_start", nt + 1, torch.int32, dev)
     scan_tmp = ws.get("scan_tmp", int(_lib.lib().amav_splat_scan_tmp_elems(nt)), torch.int32, dev)
-    ws.overflow = overflow
+    ws.overflow = overflow[:1]
 
     call("amav_splat_preprocess", dims, ptr(means3d), ptr(scales), ptr(rots), ptr(opacities), ptr(colors),
          ptr(view), ptr(proj), ptr(tanfov), ptr(geom), ptr(rect), ptr(touched), ptr(tile_count), st)

@@ -129,7 +129,8 @@ int amav_splat_preprocess(const AmavSplatDims *d, const float *means3d, const fl
  *   scan_tmp   [amav_splat_scan_tmp_elems(F*tiles)] uint32 scratch
  *   tile_cursor[F*tiles] uint32: MUST be zeroed by the caller
  *   entries    [capacity] uint64 scratch; point_list [capacity] int32 out (Gaussian index within the frame)
- *   overflow   [1] int32: set to 1 (and binning truncated) when D > capacity
+ *   overflow   [2] int32, MUST be zeroed by the caller: [0] is set to 1 (and binning truncated) when D > capacity;
+ *              [1] is the sort kernel's tile queue head
  */
 int64_t amav_splat_scan_tmp_elems(int64_t num_tiles_total);
 int amav_splat_scan(const AmavSplatDims *d, const uint32_t *tile_count, uint32_t *tile_start,
