@@ -161,6 +161,88 @@ __device__ __forceinline__ void bitonic_sort(Ptr a, int n, int logP)
 
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_CAP = 4096;     // entries sorted in shared memory (32 KB); larger buckets sort in place in L2/HBM
+constexpr int SORT_PER_THREAD = SORT_CAP / SORT_THREADS;
+constexpr int SORT_MAX_BIN = 48;
+constexpr int SORT_NET_CAP = 8192; // the same 64 KB of shared memory holds this many entries for the sorting network alone   // a depth bin fuller than this sends the tile to the bitonic network instead
+
+// One tile's bucket (n <= SORT_CAP entries in s_ent) sorted in O(n): entries are spread over B >= n depth bins
+// (bin = monotone linear map of the depth bits between the bucket's min and max), a scan of the bin counts gives
+// each bin its output range, and every bin (about one entry on average) is finished by an insertion sort on the
+// full 64-bit (depth bits, Gaussian) key.  Returns false (nothing guaranteed about s_ent's order) when the depths
+// are too clustered for that to be cheap; the caller then runs the bitonic network.
+__device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB)
+{
+    __shared__ uint32_t s_red[2 * (SORT_THREADS / 32)];
+    __shared__ uint32_t s_wsum[SORT_THREADS / 32];
+    __shared__ int s_bad;
+    const int B = 1 << logB;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t lo = 0xffffffffu, hi = 0u;
+    for (int i = threadIdx.x; i < n; i += SORT_THREADS) {
+        const uint32_t d = (uint32_t)(s_ent[i] >> 32);
+        lo = min(lo, d); hi = max(hi, d);
+    }
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
+    if (lane == 0) { s_red[warp] = lo; s_red[SORT_THREADS / 32 + warp] = hi; }
+    for (int i = threadIdx.x; i < B; i += SORT_THREADS) s_bin[i] = 0u;
+    if (threadIdx.x == 0) s_bad = 0;
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < SORT_THREADS / 32; ++w) { lo = min(lo, s_red[w]); hi = max(hi, s_red[SORT_THREADS / 32 + w]); }
+    const float scale = (float)B / ((float)(hi - lo) + 1.0f);
+    // pass 1: bin of every entry (kept in registers) + bin counts
+    uint64_t ent[SORT_PER_THREAD];
+    int bin[SORT_PER_THREAD];
+#pragma unroll
+    for (int k = 0; k < SORT_PER_THREAD; ++k) {
+        const int i = threadIdx.x + k * SORT_THREADS;
+        if (i < n) {
+            ent[k] = s_ent[i];
+            bin[k] = min(B - 1, (int)((float)((uint32_t)(ent[k] >> 32) - lo) * scale));
+            atomicAdd(&s_bin[bin[k]], 1u);
+        }
+    }
+    __syncthreads();
+    // exclusive scan of the B bin counts (B / 256 consecutive bins per thread)
+    const int per = B >> 8;                               // B >= 256 is guaranteed by the caller
+    uint32_t sum = 0, mx = 0;
+    for (int q = 0; q < per; ++q) { const uint32_t c = s_bin[threadIdx.x * per + q]; sum += c; mx = max(mx, c); }
+    if (mx > SORT_MAX_BIN) s_bad = 1;
+    const uint32_t inc = warp_inclusive_scan(sum);
+    if (lane == 31) s_wsum[warp] = inc;
+    __syncthreads();
+    if (s_bad) return false;
+    uint32_t base = inc - sum;
+#pragma unroll
+    for (int w = 0; w < SORT_THREADS / 32; ++w)
+        if (w < warp) base += s_wsum[w];
+    for (int q = 0; q < per; ++q) {
+        const uint32_t c = s_bin[threadIdx.x * per + q];
+        s_bin[threadIdx.x * per + q] = base;
+        base += c;
+    }
+    __syncthreads();
+    // pass 2: scatter (slot inside the bin from an atomic cursor: any order, the bin is sorted next)
+#pragma unroll
+    for (int k = 0; k < SORT_PER_THREAD; ++k) {
+        const int i = threadIdx.x + k * SORT_THREADS;
+        if (i < n) s_ent[atomicAdd(&s_bin[bin[k]], 1u)] = ent[k];
+    }
+    __syncthreads();
+    // pass 3: s_bin[b] is now the END of bin b; insertion sort inside each bin
+    for (int b = threadIdx.x; b < B; b += SORT_THREADS) {
+        const int e0 = b == 0 ? 0 : (int)s_bin[b - 1], e1 = (int)s_bin[b];
+        for (int i = e0 + 1; i < e1; ++i) {
+            const uint64_t x = s_ent[i];
+            int j = i - 1;
+            while (j >= e0 && s_ent[j] > x) { s_ent[j + 1] = s_ent[j]; --j; }
+            s_ent[j + 1] = x;
+        }
+    }
+    __syncthreads();
+    return true;
+}
 
 // CTAs pull tiles from a device counter (bucket sizes range from 0 to thousands of entries).
 __global__ void __launch_bounds__(SORT_THREADS) sort_tiles(unsigned int num_tiles_total,
@@ -169,7 +251,9 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_tiles(unsigned int num_tile
                                                             int32_t *__restrict__ point_list, int64_t capacity,
                                                             unsigned int *work_counter)
 {
-    __shared__ uint64_t s_ent[SORT_CAP];
+    extern __shared__ uint64_t s_sort[];
+    uint64_t *s_ent = s_sort;                                            // [SORT_CAP]
+    uint32_t *s_bin = reinterpret_cast<uint32_t *>(s_sort + SORT_CAP);   // [SORT_CAP]
     __shared__ unsigned int s_next;
     for (;;) {
         if (threadIdx.x == 0) s_next = atomicAdd(work_counter, 1u);
@@ -189,6 +273,14 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_tiles(unsigned int num_tile
         int logP = 1;
         while ((1 << logP) < n) ++logP;
         if (n <= SORT_CAP) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) s_ent[i] = entries[s + i];
+            __syncthreads();
+            if (n <= 64 || !bin_sort_tile(s_ent, s_bin, n, logP < 8 ? 8 : logP)) {
+                __syncthreads();
+                bitonic_sort(s_ent, n, logP);
+            }
+            for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
+        } else if (n <= SORT_NET_CAP) {
             for (int i = threadIdx.x; i < n; i += blockDim.x) s_ent[i] = entries[s + i];
             __syncthreads();
             bitonic_sort(s_ent, n, logP);
@@ -246,8 +338,10 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
         total, d->num_gaussians, gx, tiles, reinterpret_cast<const float4 *>(geom),
         reinterpret_cast<const ushort4 *>(rect), tile_start, tile_cursor, entries, capacity, overflow);
     AMAV_CHECK_LAUNCH();
-    const int grid = (int)(nt < AMAV_SM_COUNT * 6 ? nt : AMAV_SM_COUNT * 6);
-    sort_tiles<<<grid, SORT_THREADS, 0, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
+    const int grid = (int)(nt < AMAV_SM_COUNT * 4 ? nt : AMAV_SM_COUNT * 4);
+    const int sort_smem = SORT_NET_CAP * 8;       // >= SORT_CAP * 12
+    cudaFuncSetAttribute(sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_smem);
+    sort_tiles<<<grid, SORT_THREADS, sort_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
                                                   reinterpret_cast<unsigned int *>(overflow) + 1);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;

@@ -79,8 +79,9 @@ def test_splat_empty_and_degenerate():
 
 
 def test_splat_large_bucket_sorts_in_global_memory():
-    # > 8192 Gaussians stacked on one tile: exercises the in-place (non shared-memory) bucket sort
-    N, W, H = 9000, 32, 32
+    # > 8192 Gaussians stacked on one tile: exercises the in-place (non shared-memory) bucket sort; the other tiles
+    # hold 4096..8192 entries (sorting network in shared memory) and fewer (depth-bin sort)
+    N, W, H = 12000, 32, 32
     sc = random_scene(N, W, H, seed=5, spread=0.05, smin=0.002, smax=0.004)
     sc["opac"] *= 0.02
     view, full, tan, outs = oracle_frames(sc, H, W)
@@ -146,3 +147,18 @@ def test_bucket_overflow_is_flagged_not_fatal_and_renderer_recovers():
     Rn._WORKSPACES.clear()
     b = Rn.render_batch(gs(big), K, E, args)
     assert torch.equal(a, b)
+
+
+def test_equal_depths_fall_back_to_the_sorting_network():
+    """A fronto-parallel sheet: every Gaussian has the same depth bits, so the depth-bin sort cannot separate them and
+    the tile is sorted by the bitonic network on (depth, index); ties must come out in ascending Gaussian index."""
+    N, W, H = 1500, 64, 48
+    sc = random_scene(N, W, H, seed=21, spread=0.3, smin=0.004, smax=0.01)
+    sc["means"][:, 2] = 0.125
+    sc["E"][0, :3, :3] = torch.eye(3)
+    view, full, tan, outs = oracle_frames(sc, H, W)
+    pre, binned, img = outs[0]
+    live = pre["radii"] > 0
+    assert len(np.unique(pre["depth"][live].view(np.uint32))) == 1
+    out = _run_cuda(sc, view, full, tan, H, W, (1.0, 1.0, 1.0))
+    _check_frame(out, 0, pre, binned, img, N, H, W)
