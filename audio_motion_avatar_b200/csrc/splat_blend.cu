@@ -50,18 +50,52 @@ struct BlendParams {
 };
 
 constexpr int BLEND_THREADS = 256;
+constexpr int SUB_W = 8, SUB_H = 4;        // pixels of one warp: 8 wide x 4 tall
+
+// Upper bound of power(p) = Ah*dx^2 + Bn*dx*dy + Ch*dy^2 over the warp's pixel rectangle (dx = gx - px in
+// [dxl, dxh], dy likewise).  power is a concave quadratic with its maximum (0) at the Gaussian centre, so over a
+// box that does not contain the centre the maximum lies on the edge(s) facing it, where it is a clamped 1-D
+// quadratic optimum.  A Gaussian whose bound is below pmin (minus a rounding margin) cannot reach alpha >= 1/255
+// at any pixel of the rectangle: the exact per-pixel test would reject it 32 times, so dropping it from the
+// warp's list changes nothing in the result.
+__device__ __forceinline__ bool warp_rect_keep(const float4 a, const float4 b, float x0, float y0)
+{
+    const float Ah = a.z, Bn = a.w, Ch = b.x, pmin = b.z;
+    const float dxl = a.x - (x0 + (float)(SUB_W - 1)), dxh = a.x - x0;
+    const float dyl = a.y - (y0 + (float)(SUB_H - 1)), dyh = a.y - y0;
+    if (!(Ah < 0.0f && Ch < 0.0f)) return true;                       // degenerate conic (or NaN): exact path decides
+    const bool out_x = dxl > 0.0f || dxh < 0.0f, out_y = dyl > 0.0f || dyh < 0.0f;
+    if (!out_x && !out_y) return true;                                // centre inside the rectangle
+    const float ex = dxl > 0.0f ? dxl : dxh, ey = dyl > 0.0f ? dyl : dyh;
+    float m = -3.0e38f;
+    if (out_x) {
+        const float dy = fminf(fmaxf(__fdividef(-0.5f * Bn * ex, Ch), dyl), dyh);
+        m = fmaf(fmaf(Bn, dy, Ah * ex), ex, (Ch * dy) * dy);
+    }
+    if (out_y) {
+        const float dx = fminf(fmaxf(__fdividef(-0.5f * Bn * ey, Ah), dxl), dxh);
+        m = fmaxf(m, fmaf(fmaf(Bn, ey, Ah * dx), dx, (Ch * ey) * ey));
+    }
+    const float X = fmaxf(fabsf(dxl), fabsf(dxh)), Y = fmaxf(fabsf(dyl), fabsf(dyh));
+    const float mag = -(Ah * X * X + Ch * Y * Y);
+    return !(m + 0.01f + 8.0e-6f * mag < pmin);
+}
 
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams p, const float *__restrict__ bg)
 {
     __shared__ float4 s_g0[BLEND_THREADS];     // x, y, -conic.x/2, -conic.y
     __shared__ float4 s_g1[BLEND_THREADS];     // -conic.z/2, opacity, pmin, r
     __shared__ float4 s_g2[BLEND_THREADS];     // g, b, depth, radius
+    __shared__ unsigned char s_list[BLEND_THREADS / 32][BLEND_THREADS];   // per warp: batch entries that touch its rectangle
     __shared__ unsigned int s_next;
     const int tiles = p.gx * p.gy;
     const unsigned int total_tiles = (unsigned int)((int64_t)p.F * tiles);
     const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
-    const int lx = threadIdx.x & 15, ly = threadIdx.x >> 4;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int sx = (warp & 1) * SUB_W, sy = (warp >> 1) * SUB_H;
+    const int lx = sx + (lane & (SUB_W - 1)), ly = sy + (lane >> 3);
     const float alpha_min = 1.0f / 255.0f;
+    unsigned char *list = s_list[warp];
 
     for (;;) {
         // tiles differ in depth by orders of magnitude (the body covers ~20% of the image): CTAs pull the next
@@ -76,16 +110,17 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
         const int pxi = tx * 16 + lx, pyi = ty * 16 + ly;
         const bool inside = pxi < p.W && pyi < p.H;
         const float pxf = (float)pxi, pyf = (float)pyi;
+        const float rx0 = (float)(tx * 16 + sx), ry0 = (float)(ty * 16 + sy);
         // ranges are clamped to the caller's entry capacity: after a bucket overflow the frame is incomplete (the
         // overflow flag tells the host) but nothing is read out of bounds
         const uint32_t r0 = min(p.tile_start[t], p.capacity), r1 = min(p.tile_start[t + 1], p.capacity);
         const float4 *geom = p.geom + (int64_t)f * p.N * 3;
 
         float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dv = 0.0f;
-        int contributor = 0, last = 0;
+        int last = 0, before = 0;                 // `before`: list entries in earlier batches (upstream's contributor count)
         bool done = !inside;
         int todo = (int)(r1 - r0);
-        for (uint32_t base = r0; base < r1; base += BLEND_THREADS, todo -= BLEND_THREADS) {
+        for (uint32_t base = r0; base < r1; base += BLEND_THREADS, todo -= BLEND_THREADS, before += BLEND_THREADS) {
             if (__syncthreads_count(done) == BLEND_THREADS) break;
             if (base + threadIdx.x < r1) {
                 const int g = p.point_list[base + threadIdx.x];
@@ -96,28 +131,37 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             }
             __syncthreads();
             const int nb = todo < BLEND_THREADS ? todo : BLEND_THREADS;
-            if (!done) {
-                for (int j = 0; j < nb; ++j) {
-                    const float4 a = s_g0[j];
-                    const float4 b = s_g1[j];
-                    const float dx = a.x - pxf, dy = a.y - pyf;
-                    const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (b.x * dy) * dy);
-                    if (power > 0.0f || power < b.z) continue;          // b.z = pmin: alpha surely < 1/255
-                    const float alpha = fminf(0.99f, b.y * amav_exp(power));
-                    if (alpha < alpha_min) continue;
-                    const float Tn = T * (1.0f - alpha);
-                    if (Tn < 0.0001f) { done = true; contributor += j + 1; goto batch_done; }
-                    const float w = alpha * T;
-                    const float4 c = s_g2[j];
-                    C0 = fmaf(b.w, w, C0);
-                    C1 = fmaf(c.x, w, C1);
-                    C2 = fmaf(c.y, w, C2);
-                    if (p.out_invdepth) Dv = fmaf(1.0f / c.z, w, Dv);
-                    T = Tn;
-                    last = contributor + j + 1;
-                }
-                contributor += nb;
-            batch_done:;
+            if (__all_sync(0xffffffffu, done)) continue;
+            // 1. this warp's list: batch entries whose footprint can reach its 8x4 rectangle, in list order
+            int cnt = 0;
+            for (int j0 = 0; j0 < nb; j0 += 32) {
+                const int j = j0 + lane;
+                const bool keep = j < nb && warp_rect_keep(s_g0[j], s_g1[j], rx0, ry0);
+                const unsigned int m = __ballot_sync(0xffffffffu, keep);
+                if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned char)j;
+                cnt += __popc(m);
+            }
+            __syncwarp();
+            // 2. exact per-pixel blend over the warp's list (same arithmetic and tests as the oracle)
+            for (int k = 0; k < cnt; ++k) {
+                const int j = list[k];
+                const float4 a = s_g0[j];
+                const float4 b = s_g1[j];
+                const float dx = a.x - pxf, dy = a.y - pyf;
+                const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (b.x * dy) * dy);
+                if (done || power > 0.0f || power < b.z) continue;      // b.z = pmin: alpha surely < 1/255
+                const float alpha = fminf(0.99f, b.y * amav_exp(power));
+                if (alpha < alpha_min) continue;
+                const float Tn = T * (1.0f - alpha);
+                if (Tn < 0.0001f) { done = true; continue; }
+                const float w = alpha * T;
+                const float4 c = s_g2[j];
+                C0 = fmaf(b.w, w, C0);
+                C1 = fmaf(c.x, w, C1);
+                C2 = fmaf(c.y, w, C2);
+                if (p.out_invdepth) Dv = fmaf(1.0f / c.z, w, Dv);
+                T = Tn;
+                last = before + j + 1;
             }
         }
         if (inside) {
