@@ -54,7 +54,8 @@ def camera_matrices(K: torch.Tensor, E: torch.Tensor, height: int, width: int):
     Rt[:, :3, :3] = E[:, :3, :3]
     Rt[:, :3, 3] = E[:, :3, 3]
     Rt[:, 3, 3] = 1.0
-    view = torch.linalg.inv(torch.linalg.inv(Rt)).transpose(1, 2)
+    # inv_ex: same LU-based inverse as torch.inverse, without the host read of the `info` flag (a device sync)
+    view = torch.linalg.inv_ex(torch.linalg.inv_ex(Rt).inverse).inverse.transpose(1, 2)
     fx, fy, cx, cy = K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2]
     fovx = 2 * torch.atan(width / (2 * fx))
     fovy = 2 * torch.atan(height / (2 * fy))
@@ -93,7 +94,7 @@ def _workspace(device) -> SplatWorkspace:
 
 
 def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug, views_per_set, hwc,
-                   out=None, defer_check=False):
+                   out=None, defer_check=False, cameras=None):
     """All frames of a call in one batched splat pass.  Gaussian tensors [G,N,k] (pre-activation scale and
     opacity as in the reference's ``gaussians`` dict), cameras [G*views_per_set,...].
 
@@ -110,7 +111,7 @@ def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug,
     if dev.type != "cuda":
         raise _lib.AmavError("rendering needs CUDA tensors (no CPU path)")
     height, width = int(args.image_size[0]), int(args.image_size[1])
-    view, full, tanfov = camera_matrices(K.to(dev), E.to(dev), height, width)
+    view, full, tanfov = cameras if cameras is not None else camera_matrices(K.to(dev), E.to(dev), height, width)
     bg = _background(bg_color, dev)
     activate = True
     if debug:                                        # renderer.py:535-537
@@ -388,6 +389,8 @@ class Renderer(nn.Module):
         E = cam_params["extrinsic"].reshape(Fr, 4, 4).to(dev, non_blocking=True)
         points = self.get_smpl_vertices(params)
         transl = params["transl"].reshape(Fr, 3).float()
+        view, full, tanfov = camera_matrices(K, E, H, W)           # whole sequence at once, no per-chunk glue
+        bg = _background(None, dev)
         Wd, bd = self._decoder_wb()
         Wd, bd = Wd.detach().contiguous(), bd.detach().contiguous()
         st = self._seq_state(chunk, C, R, H, W)
@@ -414,8 +417,9 @@ class Renderer(nn.Module):
             st["tok_free"][slot] = consumed
             g = stages.sample_decode(proj, points[f0:f1], transl[f0:f1], Wd, bd, C, R, float(self.cfg.radius))
             img = st["img"][slot][:n]
-            _render_frames(g["xyz"], g["rot"], g["scale"], g["opacity"], g["color"], K[f0:f1], E[f0:f1], self.cfg,
-                           None, False, 1, True, out=img, defer_check=True)
+            _render_frames(g["xyz"], g["rot"], g["scale"], g["opacity"], g["color"], None, None, self.cfg,
+                           bg, False, 1, True, out=img, defer_check=True,
+                           cameras=(view[f0:f1], full[f0:f1], tanfov[f0:f1]))
             ws = _workspace(dev)
             pending.append((k, ws.overflow.clone() if ws.overflow is not None else None))
             rendered = torch.cuda.Event()

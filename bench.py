@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--frames", type=int, default=FRAMES)
     ap.add_argument("--gaussians", type=int, default=NGAUSS)
     ap.add_argument("--size", type=int, default=SIZE)
-    ap.add_argument("--chunk", type=int, default=8, help="frames per pipeline chunk of the e2e path")
+    ap.add_argument("--chunk", type=int, default=4, help="frames per pipeline chunk of the e2e path")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
