@@ -233,15 +233,16 @@ def run_ours(args):
     tokens, params, cams = synthetic_inputs(Fr, size, dev, seed=rank)        # each rank: its own shard of the sequence
     params_d = {k: v.to(dev) for k, v in params.items()}
     cams_d = {k: v.to(dev) for k, v in cams.items()}
+    from audio_motion_avatar_b200.shard import gather_frames
     gather_buf = None
     if world > 1 and not args.no_gather and rank == 0:
-        gather_buf = [torch.empty(1, Fr, size, size, 3, device=dev) for _ in range(world)]
+        gather_buf = torch.empty(world * Fr, size, size, 3, device=dev)
 
     def step():
         with torch.no_grad():
             img, _ = r(tokens, cams_d, None, params_d)
         if world > 1 and not args.no_gather:
-            dist.gather(img, gather_buf, dst=0)                              # frame gather over NVLink (north_star)
+            gather_frames(img[0], world * Fr, dst=0, out=gather_buf)         # frame gather over NVLink (north_star)
         return img
 
     def barrier():

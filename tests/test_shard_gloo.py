@@ -1,0 +1,63 @@
+"""Frame sharding + gather over a world_size-2 (and 3, ragged) gloo group on the CPU."""
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from audio_motion_avatar_b200.shard import frame_shard, shard_sizes
+
+
+def test_frame_shard_partitions_every_frame_once():
+    for F in (0, 1, 7, 120, 1800):
+        for world in (1, 2, 3, 4, 8):
+            cover = []
+            for r in range(world):
+                s, e = frame_shard(F, r, world)
+                assert 0 <= s <= e <= F
+                cover += list(range(s, e))
+            assert cover == list(range(F))
+            sz = shard_sizes(F, world)
+            assert sum(sz) == F and max(sz) - min(sz) <= 1
+    with pytest.raises(ValueError):
+        frame_shard(10, 2, 2)
+
+
+def _worker(rank, world, port, F, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from audio_motion_avatar_b200.shard import gather_frames, shard_inputs
+        tokens = torch.arange(F * 6, dtype=torch.float32).reshape(1, F, 2, 3)
+        cams = {"intrinsic": torch.arange(F * 9, dtype=torch.float32).reshape(1, F, 3, 3)}
+        params = {"transl": torch.arange(F * 3, dtype=torch.float32).reshape(1, F, 3)}
+        tk, cm, pr = shard_inputs(tokens, cams, params, rank, world)
+        s, e = frame_shard(F, rank, world)
+        assert tk.shape[1] == e - s and torch.equal(pr["transl"][0], params["transl"][0, s:e])
+        # "render": frame f -> an image filled with f
+        local = torch.stack([torch.full((4, 5, 3), float(f)) for f in range(s, e)]) if e > s else torch.empty(0, 4, 5, 3)
+        out = gather_frames(local, F, dst=0)
+        if rank == 0:
+            ok = out is not None and out.shape == (F, 4, 5, 3) and all(torch.all(out[f] == f) for f in range(F))
+            q.put(bool(ok))
+        else:
+            assert out is None
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,F", [(2, 120), (3, 7), (2, 1)])
+def test_gather_frames_gloo(world, F):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() + world * 17 + F) % 2000
+    procs = [ctx.Process(target=_worker, args=(r, world, port, F, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=10) is True
