@@ -14,7 +14,7 @@
  *
  * PARITY UNPINNED: the reference ships no tests, golden vectors or fixtures
  * for this path, and the upstream CUDA binary cannot be
- * built here.  The pin is: the invariants in tests/test_oracle_raster.py
+ * built here.  The pin is: the invariants in tests/test_oracle_invariants.py and tests/test_oracle_backward.py
  * (analytic single-Gaussian splat, sum of weights = 1 - final_T, finite
  * differences for the backward) and the committed tests/golden vectors.
  *
@@ -355,5 +355,219 @@ void amav_oracle_blend(int W, int H, const int32_t *ranges, const int32_t *point
                 out_color[(size_t)2 * H * W + pix] = fmaf(T, bg[2], C2);
                 if (out_invdepth) out_invdepth[pix] = Dv;
             }
+    }
+}
+
+/* ------------------------------------------------------------------ */
+/* B.1  blend backward (upstream renderCUDA of  */
+/*      backward.cu, reached through autograd from renderer.py:555-568) */
+/* ------------------------------------------------------------------ */
+/*
+ * Per pixel, back to front over the tile's list, entries with 1-based position
+ * <= n_contrib only, same skips as the forward.  Per-pair arithmetic in float as
+ * upstream; the per-Gaussian sums are kept in double (upstream uses float
+ * atomicAdd in arbitrary order, so its own result is only defined up to that
+ * rounding; gradient parity is a tolerance check).
+ *   dL_dpix [3,H,W] (CHW, gradient w.r.t. the un-clamped colour output)
+ *   dL_dmean2D [N,2] (already scaled by 0.5*W / 0.5*H as upstream), dL_dconic [N,3]
+ *   = (A, B, C) with the B entry holding HALF the true derivative (upstream
+ *   convention, undone in B.2), dL_dopacity [N], dL_dcolor [N,3].
+ */
+void amav_oracle_blend_backward(int W, int H, int N, const int32_t *ranges, const int32_t *point_list,
+                                const float *xy, const float *conic_opacity, const float *rgb,
+                                const float *bg, const float *final_T, const int32_t *n_contrib,
+                                const float *dL_dpix, float *dL_dmean2D, float *dL_dconic,
+                                float *dL_dopacity, float *dL_dcolor)
+{
+    const int gx = (W + BLOCK_X - 1) / BLOCK_X;
+    const int gy = (H + BLOCK_Y - 1) / BLOCK_Y;
+    const float alpha_min = 1.0f / 255.0f;
+    const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
+    double *acc = (double *)calloc((size_t)(N > 0 ? N : 1) * 9, sizeof(double));
+    for (int tile = 0; tile < gx * gy; ++tile) {
+        const int tx = tile % gx, ty = tile / gx;
+        const int r0 = ranges[2 * tile];
+        for (int ly = 0; ly < BLOCK_Y; ++ly)
+            for (int lx = 0; lx < BLOCK_X; ++lx) {
+                const int pxi = tx * BLOCK_X + lx, pyi = ty * BLOCK_Y + ly;
+                if (pxi >= W || pyi >= H) continue;
+                const size_t pix = (size_t)pyi * W + pxi;
+                const float pxf = (float)pxi, pyf = (float)pyi;
+                const float T_final = final_T[pix];
+                float T = T_final;
+                const int last_contributor = n_contrib[pix];
+                const float g0 = dL_dpix[pix], g1 = dL_dpix[(size_t)H * W + pix], g2 = dL_dpix[(size_t)2 * H * W + pix];
+                const float bg_dot = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
+                float accum0 = 0.0f, accum1 = 0.0f, accum2 = 0.0f, last_alpha = 0.0f;
+                float lc0 = 0.0f, lc1 = 0.0f, lc2 = 0.0f;
+                for (int k = r0 + last_contributor - 1; k >= r0; --k) {
+                    const int g = point_list[k];
+                    const float conx = conic_opacity[4 * g], cony = conic_opacity[4 * g + 1];
+                    const float conz = conic_opacity[4 * g + 2], op = conic_opacity[4 * g + 3];
+                    const float Ah = -0.5f * conx, Bn = -cony, Ch = -0.5f * conz;
+                    const float dx = xy[2 * g] - pxf, dy = xy[2 * g + 1] - pyf;
+                    const float power = fmaf(fmaf(Bn, dy, Ah * dx), dx, (Ch * dy) * dy);
+                    if (power > 0.0f) continue;
+                    const float G = amav_oracle_exp(power);
+                    const float alpha = fminf(0.99f, op * G);
+                    if (alpha < alpha_min) continue;
+                    T = T / (1.0f - alpha);
+                    const float w = alpha * T;
+                    float dL_dalpha = 0.0f;
+                    accum0 = last_alpha * lc0 + (1.0f - last_alpha) * accum0; lc0 = rgb[3 * g];
+                    accum1 = last_alpha * lc1 + (1.0f - last_alpha) * accum1; lc1 = rgb[3 * g + 1];
+                    accum2 = last_alpha * lc2 + (1.0f - last_alpha) * accum2; lc2 = rgb[3 * g + 2];
+                    dL_dalpha += (lc0 - accum0) * g0;
+                    dL_dalpha += (lc1 - accum1) * g1;
+                    dL_dalpha += (lc2 - accum2) * g2;
+                    dL_dalpha *= T;
+                    last_alpha = alpha;
+                    dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
+                    const float dL_dG = op * dL_dalpha;
+                    const float gdx = G * dx, gdy = G * dy;
+                    const float dG_ddelx = -gdx * conx - gdy * cony;
+                    const float dG_ddely = -gdy * conz - gdx * cony;
+                    double *a = acc + (size_t)g * 9;
+                    a[0] += (double)(dL_dG * dG_ddelx * ddelx_dx);
+                    a[1] += (double)(dL_dG * dG_ddely * ddely_dy);
+                    a[2] += (double)(-0.5f * gdx * dx * dL_dG);
+                    a[3] += (double)(-0.5f * gdx * dy * dL_dG);
+                    a[4] += (double)(-0.5f * gdy * dy * dL_dG);
+                    a[5] += (double)(G * dL_dalpha);
+                    a[6] += (double)(w * g0);
+                    a[7] += (double)(w * g1);
+                    a[8] += (double)(w * g2);
+                }
+            }
+    }
+    for (int i = 0; i < N; ++i) {
+        const double *a = acc + (size_t)i * 9;
+        dL_dmean2D[2 * i] = (float)a[0]; dL_dmean2D[2 * i + 1] = (float)a[1];
+        dL_dconic[3 * i] = (float)a[2]; dL_dconic[3 * i + 1] = (float)a[3]; dL_dconic[3 * i + 2] = (float)a[4];
+        dL_dopacity[i] = (float)a[5];
+        dL_dcolor[3 * i] = (float)a[6]; dL_dcolor[3 * i + 1] = (float)a[7]; dL_dcolor[3 * i + 2] = (float)a[8];
+    }
+    free(acc);
+}
+
+/* ------------------------------------------------------------------ */
+/* B.2-B.4  per-Gaussian backward: conic -> cov2D -> (cov3D, view-space */
+/*          point) -> (scale, rotation, mean3D); mean2D -> mean3D       */
+/* ------------------------------------------------------------------ */
+/*
+ * Follows upstream computeCov2DCUDA / preprocessCUDA / computeCov3D of backward.cu:
+ *   - denom2inv = 1/(det^2 + 1e-7);
+ *   - where t.x/t.z (t.y/t.z) was clamped to +-1.3 tanfov the x (y) gradient is masked and the
+ *     clamped value is treated as independent of t.z (upstream's approximation);
+ *   - the quaternion is not normalised (gradient of the raw quaternion -> matrix map).
+ * Inputs are the forward's inputs plus radii (> 0 selects the Gaussians that were rendered).
+ * Outputs dL_dmeans3d [N,3], dL_dscales [N,3], dL_drots [N,4] are overwritten.
+ */
+void amav_oracle_preprocess_backward(
+    int N, const float *means3d, const float *scales, const float *rots,
+    const float *view, const float *proj, int W, int H, float tanfovx, float tanfovy,
+    float scale_modifier, const int32_t *radii, const float *dL_dmean2D, const float *dL_dconic,
+    float *dL_dmeans3d, float *dL_dscales, float *dL_drots)
+{
+    const float focal_x = (float)W / (2.0f * tanfovx);
+    const float focal_y = (float)H / (2.0f * tanfovy);
+    const float limx = 1.3f * tanfovx;
+    const float limy = 1.3f * tanfovy;
+    for (int i = 0; i < N; ++i) {
+        for (int k = 0; k < 3; ++k) { dL_dmeans3d[3 * i + k] = 0.0f; dL_dscales[3 * i + k] = 0.0f; }
+        for (int k = 0; k < 4; ++k) dL_drots[4 * i + k] = 0.0f;
+        if (radii[i] <= 0) continue;
+        const float px = means3d[3 * i], py = means3d[3 * i + 1], pz = means3d[3 * i + 2];
+        const float pvx = view[0] * px + view[4] * py + view[8] * pz + view[12];
+        const float pvy = view[1] * px + view[5] * py + view[9] * pz + view[13];
+        const float pvz = view[2] * px + view[6] * py + view[10] * pz + view[14];
+        /* forward quantities again (same expressions as amav_oracle_preprocess) */
+        const float s[3] = {scale_modifier * scales[3 * i], scale_modifier * scales[3 * i + 1], scale_modifier * scales[3 * i + 2]};
+        const float qr = rots[4 * i], qx = rots[4 * i + 1], qy = rots[4 * i + 2], qz = rots[4 * i + 3];
+        float Rm[3][3];
+        Rm[0][0] = 1.0f - 2.0f * (qy * qy + qz * qz); Rm[0][1] = 2.0f * (qx * qy - qr * qz); Rm[0][2] = 2.0f * (qx * qz + qr * qy);
+        Rm[1][0] = 2.0f * (qx * qy + qr * qz); Rm[1][1] = 1.0f - 2.0f * (qx * qx + qz * qz); Rm[1][2] = 2.0f * (qy * qz - qr * qx);
+        Rm[2][0] = 2.0f * (qx * qz - qr * qy); Rm[2][1] = 2.0f * (qy * qz + qr * qx); Rm[2][2] = 1.0f - 2.0f * (qx * qx + qy * qy);
+        float m[3][3], S[3][3];
+        for (int a = 0; a < 3; ++a) for (int k = 0; k < 3; ++k) m[a][k] = Rm[a][k] * s[k];
+        for (int a = 0; a < 3; ++a) for (int b = 0; b < 3; ++b) S[a][b] = m[a][0] * m[b][0] + m[a][1] * m[b][1] + m[a][2] * m[b][2];
+        const float txtz = pvx / pvz, tytz = pvy / pvz;
+        const float txc = fminf(limx, fmaxf(-limx, txtz)) * pvz;
+        const float tyc = fminf(limy, fmaxf(-limy, tytz)) * pvz;
+        const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.0f : 1.0f;
+        const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.0f : 1.0f;
+        const float J00 = focal_x / pvz, J02 = -(focal_x * txc) / (pvz * pvz);
+        const float J11 = focal_y / pvz, J12 = -(focal_y * tyc) / (pvz * pvz);
+        float A0[3], A1[3], u[3], v[3];
+        for (int k = 0; k < 3; ++k) {              /* Rv[r][k] = view[k*4 + r] */
+            A0[k] = J00 * view[k * 4] + J02 * view[k * 4 + 2];
+            A1[k] = J11 * view[k * 4 + 1] + J12 * view[k * 4 + 2];
+        }
+        for (int k = 0; k < 3; ++k) {
+            u[k] = A0[0] * S[0][k] + A0[1] * S[1][k] + A0[2] * S[2][k];
+            v[k] = A1[0] * S[0][k] + A1[1] * S[1][k] + A1[2] * S[2][k];
+        }
+        const float a = (u[0] * A0[0] + u[1] * A0[1] + u[2] * A0[2]) + 0.3f;
+        const float b = u[0] * A1[0] + u[1] * A1[1] + u[2] * A1[2];
+        const float c = (v[0] * A1[0] + v[1] * A1[1] + v[2] * A1[2]) + 0.3f;
+        /* B.2: conic -> (a, b, c) */
+        const float X = dL_dconic[3 * i], Y = dL_dconic[3 * i + 1], Z = dL_dconic[3 * i + 2];
+        const float denom = a * c - b * b;
+        const float denom2inv = 1.0f / (denom * denom + 0.0000001f);
+        float dL_da = 0.0f, dL_db = 0.0f, dL_dc = 0.0f;
+        if (denom2inv != 0.0f) {
+            dL_da = denom2inv * (-c * c * X + 2.0f * b * c * Y + (denom - a * c) * Z);
+            dL_dc = denom2inv * (-a * a * Z + 2.0f * a * b * Y + (denom - a * c) * X);
+            dL_db = denom2inv * 2.0f * (b * c * X - (denom + 2.0f * b * b) * Y + a * b * Z);
+        }
+        /* (a, b, c) -> Sigma (full symmetric gradient Gs) and -> A */
+        float Gs[3][3];
+        for (int k = 0; k < 3; ++k)
+            for (int l = 0; l < 3; ++l)
+                Gs[k][l] = A0[k] * A0[l] * dL_da + 0.5f * (A0[k] * A1[l] + A0[l] * A1[k]) * dL_db + A1[k] * A1[l] * dL_dc;
+        float dA0[3], dA1[3];
+        for (int k = 0; k < 3; ++k) {
+            dA0[k] = 2.0f * u[k] * dL_da + v[k] * dL_db;
+            dA1[k] = 2.0f * v[k] * dL_dc + u[k] * dL_db;
+        }
+        float dJ00 = 0.0f, dJ02 = 0.0f, dJ11 = 0.0f, dJ12 = 0.0f;
+        for (int k = 0; k < 3; ++k) {
+            dJ00 += view[k * 4] * dA0[k];
+            dJ02 += view[k * 4 + 2] * dA0[k];
+            dJ11 += view[k * 4 + 1] * dA1[k];
+            dJ12 += view[k * 4 + 2] * dA1[k];
+        }
+        const float tz = 1.0f / pvz, tz2 = tz * tz, tz3 = tz2 * tz;
+        const float dL_dtx = x_grad_mul * -focal_x * tz2 * dJ02;
+        const float dL_dty = y_grad_mul * -focal_y * tz2 * dJ12;
+        const float dL_dtz = -focal_x * tz2 * dJ00 - focal_y * tz2 * dJ11 + (2.0f * focal_x * txc) * tz3 * dJ02 +
+                             (2.0f * focal_y * tyc) * tz3 * dJ12;
+        float dmean[3];
+        for (int k = 0; k < 3; ++k) dmean[k] = view[k * 4] * dL_dtx + view[k * 4 + 1] * dL_dty + view[k * 4 + 2] * dL_dtz;
+        /* B.3: mean2D (NDC-scaled) -> mean3D */
+        const float phx = proj[0] * px + proj[4] * py + proj[8] * pz + proj[12];
+        const float phy = proj[1] * px + proj[5] * py + proj[9] * pz + proj[13];
+        const float phw = proj[3] * px + proj[7] * py + proj[11] * pz + proj[15];
+        const float m_w = 1.0f / (phw + 0.0000001f);
+        const float mul1 = phx * m_w * m_w, mul2 = phy * m_w * m_w;
+        const float d2x = dL_dmean2D[2 * i], d2y = dL_dmean2D[2 * i + 1];
+        for (int k = 0; k < 3; ++k)
+            dmean[k] += (proj[k * 4] * m_w - proj[k * 4 + 3] * mul1) * d2x + (proj[k * 4 + 1] * m_w - proj[k * 4 + 3] * mul2) * d2y;
+        for (int k = 0; k < 3; ++k) dL_dmeans3d[3 * i + k] = dmean[k];
+        /* B.4: Sigma = m m^T, m[a][k] = Rot[a][k] s_k */
+        float dm[3][3], D[3][3];
+        for (int a2 = 0; a2 < 3; ++a2)
+            for (int k = 0; k < 3; ++k)
+                dm[a2][k] = 2.0f * (Gs[a2][0] * m[0][k] + Gs[a2][1] * m[1][k] + Gs[a2][2] * m[2][k]);
+        for (int k = 0; k < 3; ++k)
+            dL_dscales[3 * i + k] = (dm[0][k] * Rm[0][k] + dm[1][k] * Rm[1][k] + dm[2][k] * Rm[2][k]) * scale_modifier;
+        for (int a2 = 0; a2 < 3; ++a2) for (int k = 0; k < 3; ++k) D[a2][k] = dm[a2][k] * s[k];
+        dL_drots[4 * i] = 2.0f * (-qz * D[0][1] + qy * D[0][2] + qz * D[1][0] - qx * D[1][2] - qy * D[2][0] + qx * D[2][1]);
+        dL_drots[4 * i + 1] = 2.0f * (qy * D[0][1] + qz * D[0][2] + qy * D[1][0] - 2.0f * qx * D[1][1] - qr * D[1][2] +
+                                      qz * D[2][0] + qr * D[2][1] - 2.0f * qx * D[2][2]);
+        dL_drots[4 * i + 2] = 2.0f * (-2.0f * qy * D[0][0] + qx * D[0][1] + qr * D[0][2] + qx * D[1][0] + qz * D[1][2] -
+                                      qr * D[2][0] + qz * D[2][1] - 2.0f * qy * D[2][2]);
+        dL_drots[4 * i + 3] = 2.0f * (-2.0f * qz * D[0][0] - qr * D[0][1] + qx * D[0][2] + qr * D[1][0] - 2.0f * qz * D[1][1] +
+                                      qy * D[1][2] + qx * D[2][0] + qy * D[2][1]);
     }
 }

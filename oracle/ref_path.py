@@ -346,3 +346,61 @@ def reference_frames(model, weights, tokens, params, K, E, height, width, channe
     g = construct_gaussians(decode_heads(pts, feats, weights), pts, params["transl"])
     imgs = [render_one({k: v[f] for k, v in g.items()}, K[f], E[f], height, width, bg).permute(1, 2, 0) for f in range(Fr)]
     return torch.stack(imgs), g
+
+
+# ----------------------------------------------------------------------------------------
+# a-10  rasteriser backward: ctypes binding of the C restatement
+# ----------------------------------------------------------------------------------------
+def raster_backward(means3d, scales, rots, opacities, colors, view, proj, tanfovx, tanfovy, bg, W, H,
+                    pre, binned, out, dL_dcolor_out, scale_modifier=1.0):
+    """Gradients of a scalar loss w.r.t. the rasteriser's inputs (activated scales/opacities, colours_precomp)
+    given dL/d(colour output) [3,H,W] and the forward's (pre, binned, out) dicts.  Returns a dict with
+    means3d [N,3], scales [N,3], rots [N,4], opacities [N,1], colors [N,3] plus the screen-space sums
+    mean2d [N,2], conic [N,3]."""
+    m, s, r = _f32(means3d), _f32(scales), _f32(rots)
+    v, p = _f32(view).reshape(16), _f32(proj).reshape(16)
+    rgb, bgc, g = _f32(colors), _f32(bg), _f32(dL_dcolor_out)
+    N = m.shape[0]
+    d2 = np.zeros((N, 2), np.float32); dcon = np.zeros((N, 3), np.float32)
+    dop = np.zeros(N, np.float32); dcol = np.zeros((N, 3), np.float32)
+    pl = binned["point_list"] if binned["D"] > 0 else np.zeros(1, np.int32)
+    _lib().amav_oracle_blend_backward(
+        ctypes.c_int(W), ctypes.c_int(H), ctypes.c_int(N), _p(binned["ranges"]), _p(pl), _p(pre["xy"]),
+        _p(pre["conic_opacity"]), _p(rgb), _p(bgc), _p(out["final_T"]), _p(out["n_contrib"]), _p(g),
+        _p(d2), _p(dcon), _p(dop), _p(dcol))
+    dm = np.zeros((N, 3), np.float32); ds = np.zeros((N, 3), np.float32); dr = np.zeros((N, 4), np.float32)
+    _lib().amav_oracle_preprocess_backward(
+        ctypes.c_int(N), _p(m), _p(s), _p(r), _p(v), _p(p), ctypes.c_int(W), ctypes.c_int(H),
+        ctypes.c_float(tanfovx), ctypes.c_float(tanfovy), ctypes.c_float(scale_modifier), _p(pre["radii"]),
+        _p(d2), _p(dcon), _p(dm), _p(ds), _p(dr))
+    return dict(means3d=dm, scales=ds, rots=dr, opacities=dop.reshape(N, 1), colors=dcol, mean2d=d2, conic=dcon)
+
+
+class _OracleRaster(torch.autograd.Function):
+    """One frame of the C rasteriser as an autograd node (forward = amav_oracle_*, backward = Appendix B), so the
+    oracle's full path (LBS -> query -> decode -> activations -> rasteriser) is differentiable on the CPU the way
+    the reference's is through diff_gaussian_rasterization's autograd Function."""
+
+    @staticmethod
+    def forward(ctx, means3d, scales, rots, opacities, colors, view, proj, tanfovx, tanfovy, bg, W, H):
+        pre, binned, out = rasterize(means3d, scales, rots, opacities, colors, view, proj, tanfovx, tanfovy, bg, W, H)
+        ctx.save_for_backward(means3d, scales, rots, opacities, colors, view, proj)
+        ctx.misc = (tanfovx, tanfovy, bg, W, H, pre, binned, out)
+        return torch.from_numpy(out["color"].copy())
+
+    @staticmethod
+    def backward(ctx, grad):
+        means3d, scales, rots, opacities, colors, view, proj = ctx.saved_tensors
+        tanfovx, tanfovy, bg, W, H, pre, binned, out = ctx.misc
+        g = raster_backward(means3d, scales, rots, opacities, colors, view, proj, tanfovx, tanfovy, bg, W, H,
+                            pre, binned, out, grad.contiguous())
+        t = lambda k: torch.from_numpy(g[k])
+        return (t("means3d"), t("scales"), t("rots"), t("opacities"), t("colors"), None, None, None, None, None, None, None)
+
+
+def render_one_autograd(g_frame: Dict[str, torch.Tensor], K, E, height, width, bg=(1.0, 1.0, 1.0)) -> torch.Tensor:
+    """render_one (renderer.py:481-570) for one frame with gradients to the Gaussian attributes; [3,H,W] in [0,1]."""
+    view, full, tfx, tfy, _ = camera_setup(K, E, height, width)
+    scales, opac, col = activate_for_raster(g_frame)
+    img = _OracleRaster.apply(g_frame["xyz"], scales, g_frame["rot"], opac, col, view, full, tfx, tfy, bg, width, height)
+    return img.clamp(0, 1)
