@@ -17,6 +17,8 @@ SOURCES = [
     ("splat_preprocess.cu", ["-fmad=false"]),
     ("splat_bin.cu", []),
     ("splat_blend.cu", ["-fmad=false"]),
+    ("splat_blend_bwd.cu", ["-fmad=false"]),
+    ("splat_preprocess_bwd.cu", []),
     ("triplane.cu", []),
     ("lbs.cu", []),
 ]

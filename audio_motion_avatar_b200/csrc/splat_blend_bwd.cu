@@ -1,0 +1,247 @@
+// Stage 4c backward: gradient of the blend w.r.t. the screen-space Gaussian records (upstream renderCUDA of
+// backward.cu; reached in the reference through autograd of the GaussianRasterizer
+// call at src/models/renderer.py:555-566).
+//
+// Compiled with -fmad=false and sharing amav_exp / the power expression with the forward kernel, so every
+// (pixel, Gaussian) pair takes the same skip decisions here as it did in the forward pass.
+//
+// Upstream issues 9 global float atomicAdds per contributing (pixel, Gaussian) pair.  Here:
+//   * persistent CTAs pull tiles from a device queue (same imbalance as the forward);
+//   * a tile starts at the deepest list position any of its pixels reached (max n_contrib), not at the list end;
+//   * each warp owns an 8x4 pixel rectangle and culls every 256-entry batch against it (same exact bound as the
+//     forward), walks its list back to front, reduces the 9 per-pair terms over its 32 pixels with a 14-shuffle
+//     split butterfly, and adds them to a per-batch accumulator in shared memory;
+//   * after a batch the CTA flushes one record per (tile, Gaussian) with two float4 + one scalar global
+//     reductions: ~1 global atomic record per (tile, Gaussian) instead of 9 per (pixel, Gaussian).
+#include "blend_common.cuh"
+
+namespace {
+
+using namespace amav_blend;
+
+struct BlendBwdParams {
+    int F, N, W, H, gx, gy, hwc;
+    const float4 *geom;
+    const uint32_t *tile_start;
+    const int32_t *point_list;
+    const float *final_T;
+    const int32_t *n_contrib;
+    const float *dL_dpix;
+    float *dsum;                     // [F,N,12]: mean2D.xy (x 0.5W, 0.5H), conic A B C, opacity, rgb, 3 pad
+    unsigned int *work_counter;
+    uint32_t capacity;
+};
+
+constexpr int NV = 9;                // accumulated values per Gaussian
+constexpr int ACC_LD = 9;            // row stride of the smem accumulator (odd: conflict-free flush)
+
+__global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendBwdParams p, const float *__restrict__ bg)
+{
+    __shared__ float4 s_g0[BLEND_THREADS];
+    __shared__ float4 s_g1[BLEND_THREADS];
+    __shared__ float4 s_g2[BLEND_THREADS];
+    __shared__ float s_acc[BLEND_THREADS * ACC_LD];
+    __shared__ int s_gid[BLEND_THREADS];
+    __shared__ unsigned char s_list[BLEND_THREADS / 32][BLEND_THREADS];
+    __shared__ unsigned int s_next;
+    __shared__ int s_maxc;
+    const int tiles = p.gx * p.gy;
+    const unsigned int total_tiles = (unsigned int)((int64_t)p.F * tiles);
+    const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int sx = (warp & 1) * SUB_W, sy = (warp >> 1) * SUB_H;
+    const int lx = sx + (lane & (SUB_W - 1)), ly = sy + (lane >> 3);
+    const float alpha_min = 1.0f / 255.0f;
+    const float ddelx_dx = 0.5f * (float)p.W, ddely_dy = 0.5f * (float)p.H;
+    unsigned char *list = s_list[warp];
+    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4;
+    const int my_slot = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    const int64_t hw = (int64_t)p.H * p.W;
+
+    for (;;) {
+        if (threadIdx.x == 0) { s_next = atomicAdd(p.work_counter, 1u); s_maxc = 0; }
+        __syncthreads();
+        const unsigned int t = s_next;
+        if (t >= total_tiles) break;
+        const int f = (int)(t / tiles);
+        const int tile = (int)(t - (unsigned int)f * tiles);
+        const int ty = tile / p.gx, tx = tile - ty * p.gx;
+        const int pxi = tx * 16 + lx, pyi = ty * 16 + ly;
+        const bool inside = pxi < p.W && pyi < p.H;
+        const float pxf = (float)pxi, pyf = (float)pyi;
+        const float rx0 = (float)(tx * 16 + sx), ry0 = (float)(ty * 16 + sy);
+        const uint32_t r0 = min(p.tile_start[t], p.capacity), r1 = min(p.tile_start[t + 1], p.capacity);
+        const float4 *geom = p.geom + (int64_t)f * p.N * 3;
+        float *dsum = p.dsum + (int64_t)f * p.N * 12;
+
+        float T_final = 1.0f, g0 = 0.0f, g1 = 0.0f, g2 = 0.0f;
+        int last_contributor = 0;
+        if (inside) {
+            const int64_t pix = (int64_t)pyi * p.W + pxi;
+            T_final = p.final_T[(int64_t)f * hw + pix];
+            last_contributor = p.n_contrib[(int64_t)f * hw + pix];
+            if (p.hwc) {
+                const float *g = p.dL_dpix + ((int64_t)f * hw + pix) * 3;
+                g0 = g[0]; g1 = g[1]; g2 = g[2];
+            } else {
+                const float *g = p.dL_dpix + (int64_t)f * 3 * hw + pix;
+                g0 = g[0]; g1 = g[hw]; g2 = g[2 * hw];
+            }
+        }
+        int wmax = last_contributor;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, d));
+        if (lane == 0 && wmax > 0) atomicMax(&s_maxc, wmax);
+        __syncthreads();
+        const int nproc = min(s_maxc, (int)(r1 - r0));
+        const float bg_dot = bg0 * g0 + bg1 * g1 + bg2 * g2;
+        float T = T_final, accum0 = 0.0f, accum1 = 0.0f, accum2 = 0.0f, last_alpha = 0.0f;
+        float lc0 = 0.0f, lc1 = 0.0f, lc2 = 0.0f;
+
+        for (int b = (nproc - 1) >> 8; b >= 0 && nproc > 0; --b) {
+            const int before = b * BLEND_THREADS;
+            const int nb = min(BLEND_THREADS, nproc - before);
+            __syncthreads();                                   // previous batch's flush has drained s_acc / s_g*
+            if ((int)threadIdx.x < nb) {
+                const int g = p.point_list[r0 + before + threadIdx.x];
+                const float4 *src = geom + 3 * (int64_t)g;
+                s_g0[threadIdx.x] = src[0];
+                s_g1[threadIdx.x] = src[1];
+                s_g2[threadIdx.x] = src[2];
+                s_gid[threadIdx.x] = g;
+            }
+#pragma unroll
+            for (int k = 0; k < ACC_LD; ++k) s_acc[threadIdx.x * ACC_LD + k] = 0.0f;
+            __syncthreads();
+            // this warp's list for the batch (list order), entries beyond the warp's deepest contributor dropped
+            int cnt = 0;
+            if (wmax > before) {
+                const int lim = min(nb, wmax - before);
+                for (int j0 = 0; j0 < lim; j0 += 32) {
+                    const int j = j0 + lane;
+                    const bool keep = j < lim && warp_rect_keep(s_g0[j], s_g1[j], rx0, ry0);
+                    const unsigned int m = __ballot_sync(0xffffffffu, keep);
+                    if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned char)j;
+                    cnt += __popc(m);
+                }
+            }
+            __syncwarp();
+            for (int k = cnt - 1; k >= 0; --k) {
+                const int j = list[k];
+                const float4 a = s_g0[j];
+                const float4 bq = s_g1[j];
+                const float dx = a.x - pxf, dy = a.y - pyf;
+                const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (bq.x * dy) * dy);
+                bool use = (before + j + 1 <= last_contributor) && !(power > 0.0f) && !(power < bq.z);
+                float G = 0.0f, alpha = 0.0f;
+                if (use) {
+                    G = amav_exp(power);
+                    alpha = fminf(0.99f, bq.y * G);
+                    use = !(alpha < alpha_min);
+                }
+                if (!__any_sync(0xffffffffu, use)) continue;
+                float v[8], v8 = 0.0f;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) v[q] = 0.0f;
+                if (use) {
+                    const float4 c = s_g2[j];
+                    const float om = 1.0f - alpha;
+                    T = T / om;
+                    const float w = alpha * T;
+                    accum0 = fmaf(last_alpha, lc0, (1.0f - last_alpha) * accum0); lc0 = bq.w;
+                    accum1 = fmaf(last_alpha, lc1, (1.0f - last_alpha) * accum1); lc1 = c.x;
+                    accum2 = fmaf(last_alpha, lc2, (1.0f - last_alpha) * accum2); lc2 = c.y;
+                    float dL_dalpha = (lc0 - accum0) * g0;
+                    dL_dalpha = fmaf(lc1 - accum1, g1, dL_dalpha);
+                    dL_dalpha = fmaf(lc2 - accum2, g2, dL_dalpha);
+                    dL_dalpha = dL_dalpha * T;
+                    last_alpha = alpha;
+                    dL_dalpha = fmaf(-T_final / om, bg_dot, dL_dalpha);
+                    const float dL_dG = bq.y * dL_dalpha;
+                    const float gdx = G * dx, gdy = G * dy;
+                    // conic = (-2 Ah, -Bn, -2 Ch): dG/ddelx = -gdx*conic.x - gdy*conic.y
+                    const float dG_ddelx = fmaf(2.0f * a.z, gdx, a.w * gdy);
+                    const float dG_ddely = fmaf(2.0f * bq.x, gdy, a.w * gdx);
+                    const float hq = -0.5f * dL_dG;
+                    v[0] = dL_dG * dG_ddelx * ddelx_dx;
+                    v[1] = dL_dG * dG_ddely * ddely_dy;
+                    v[2] = hq * gdx * dx;
+                    v[3] = hq * gdx * dy;
+                    v[4] = hq * gdy * dy;
+                    v[5] = G * dL_dalpha;
+                    v[6] = w * g0;
+                    v[7] = w * g1;
+                    v8 = w * g2;
+                }
+                // split butterfly: 8 values over 32 lanes in 4+2+1+1+1 shuffles, the ninth in 5
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float send = upper16 ? v[q] : v[q + 4];
+                    const float keep = upper16 ? v[q + 4] : v[q];
+                    v[q] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                }
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const float send = upper8 ? v[q] : v[q + 2];
+                    const float keep = upper8 ? v[q + 2] : v[q];
+                    v[q] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
+                {
+                    const float send = upper4 ? v[0] : v[1];
+                    const float keep = upper4 ? v[1] : v[0];
+                    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                }
+                v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+                v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, d);
+                if ((lane & 3) == 0) atomicAdd(&s_acc[j * ACC_LD + my_slot], v[0]);
+                else if (lane == 1) atomicAdd(&s_acc[j * ACC_LD + 8], v8);
+            }
+            __syncthreads();
+            // flush: one record per (tile, Gaussian)
+            if ((int)threadIdx.x < nb) {
+                const float *s = s_acc + threadIdx.x * ACC_LD;
+                const float4 q0 = make_float4(s[0], s[1], s[2], s[3]);
+                const float4 q1 = make_float4(s[4], s[5], s[6], s[7]);
+                const float q2 = s[8];
+                const bool nz = q0.x != 0.0f || q0.y != 0.0f || q0.z != 0.0f || q0.w != 0.0f || q1.x != 0.0f ||
+                                q1.y != 0.0f || q1.z != 0.0f || q1.w != 0.0f || q2 != 0.0f;
+                if (nz) {
+                    float *dst = dsum + (int64_t)s_gid[threadIdx.x] * 12;
+                    atomicAdd(reinterpret_cast<float4 *>(dst), q0);
+                    atomicAdd(reinterpret_cast<float4 *>(dst) + 1, q1);
+                    atomicAdd(dst + 8, q2);
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+extern "C" int amav_splat_blend_backward(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
+                                         const int32_t *point_list, int64_t capacity, const float *bg, int hwc,
+                                         const float *final_T, const int32_t *n_contrib, const float *dL_dcolor,
+                                         float *dsum, uint32_t *work_counter, void *stream)
+{
+    AMAV_CHECK_ARG(d && d->frames >= 0 && d->width > 0 && d->height > 0, "bad dims");
+    if (d->frames == 0) return AMAV_OK;
+    AMAV_CHECK_ARG(tile_start && bg && final_T && n_contrib && dL_dcolor && dsum && work_counter, "null buffer");
+    AMAV_CHECK_ARG(((uintptr_t)dsum & 15) == 0, "dsum must be 16-byte aligned");
+    AMAV_CHECK_ARG(capacity >= 0, "bad capacity");
+    BlendBwdParams p;
+    p.F = d->frames; p.N = d->num_gaussians; p.W = d->width; p.H = d->height;
+    p.gx = (d->width + 15) / 16; p.gy = (d->height + 15) / 16; p.hwc = hwc;
+    p.geom = reinterpret_cast<const float4 *>(geom); p.tile_start = tile_start; p.point_list = point_list;
+    p.final_T = final_T; p.n_contrib = n_contrib; p.dL_dpix = dL_dcolor; p.dsum = dsum;
+    p.work_counter = work_counter;
+    p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity;
+    const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;
+    AMAV_CHECK_ARG(total_tiles < ((int64_t)1 << 31), "too many tiles");
+    const int grid = (int)(total_tiles < AMAV_SM_COUNT * 6 ? total_tiles : AMAV_SM_COUNT * 6);
+    blend_bwd_kernel<<<grid, BLEND_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
+    AMAV_CHECK_LAUNCH();
+    return AMAV_OK;
+}

@@ -122,3 +122,71 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     return {"color": out, "geom": geom.view(F, N, 12), "rect": rect.view(F, N, 4), "tiles_touched": touched.view(F, N),
             "tile_start": tile_start, "point_list": ws.point_list, "D": D, "final_T": final_T,
             "n_contrib": n_contrib, "invdepth": invdepth, "workspace": ws}
+
+
+def splat_backward(fwd: Dict[str, torch.Tensor], grad_color: torch.Tensor, means3d, scales, rots, opacities, colors,
+                   view, proj, tanfov, bg, height: int, width: int, *, views_per_set: int = 1, activate: bool = False,
+                   hwc: bool = False, scale_modifier: float = 1.0) -> Dict[str, torch.Tensor]:
+    """Gradients of the splat inputs from dL/d(colour output): blend backward (per-(frame, Gaussian) screen-space
+    sums) then the per-Gaussian chain.  ``fwd`` is the dict ``splat_forward(..., want_aux=True)`` returned (its
+    buffers must still hold that call's data).  Replaces _RasterizeGaussians.backward + the autograd of render_one's
+    activations (renderer.py:532-533,547,555-568)."""
+    dev = grad_color.device
+    F = int(view.shape[0])
+    N = int(means3d.shape[-2])
+    G = F // views_per_set
+    f32 = lambda t: t.detach().to(torch.float32).contiguous()
+    means3d, scales, rots, opacities, colors = map(f32, (means3d, scales, rots, opacities, colors))
+    view, proj, tanfov, bg, grad_color = map(f32, (view, proj, tanfov, bg, grad_color))
+    dims = SplatDims(F, N, views_per_set, width, height, int(activate), float(scale_modifier))
+    st = stream_ptr()
+    dsum = torch.zeros(F, N, 12, dtype=torch.float32, device=dev)
+    counter = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws = fwd["workspace"]
+    geom = fwd["geom"].reshape(-1)
+    call("amav_splat_blend_backward", dims, ptr(geom), ptr(fwd["tile_start"]), ptr(fwd["point_list"]), ws.capacity,
+         ptr(bg), int(hwc), ptr(fwd["final_T"]), ptr(fwd["n_contrib"]), ptr(grad_color), ptr(dsum), ptr(counter), st)
+    d_means = torch.empty(G, N, 3, device=dev)
+    d_scales = torch.empty(G, N, 3, device=dev)
+    d_rots = torch.empty(G, N, 4, device=dev)
+    d_opac = torch.empty(G, N, 1, device=dev)
+    d_colors = torch.empty(G, N, 3, device=dev)
+    call("amav_splat_preprocess_backward", dims, ptr(means3d), ptr(scales), ptr(rots), ptr(opacities), ptr(colors),
+         ptr(view), ptr(proj), ptr(tanfov), ptr(geom), ptr(dsum), ptr(d_means), ptr(d_scales), ptr(d_rots),
+         ptr(d_opac), ptr(d_colors), st)
+    return {"means3d": d_means, "scales": d_scales, "rots": d_rots, "opacities": d_opac, "colors": d_colors, "dsum": dsum}
+
+
+class SplatFunction(torch.autograd.Function):
+    """Differentiable batched splat: forward = splat_forward (own workspace, aux kept), backward = splat_backward.
+    Cameras, background and the image size carry no gradient (as in the reference, where they are plain settings)."""
+
+    @staticmethod
+    def forward(ctx, means3d, scales, rots, opacities, colors, view, proj, tanfov, bg, height, width, views_per_set,
+                activate, hwc, clamp01, scale_modifier):
+        ws = SplatWorkspace()
+        fwd = splat_forward(means3d, scales, rots, opacities, colors, view, proj, tanfov, bg, height, width,
+                            views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=clamp01, want_aux=True,
+                            scale_modifier=scale_modifier, workspace=ws)
+        ctx.fwd = fwd
+        ctx.args = (height, width, views_per_set, activate, hwc, scale_modifier)
+        ctx.save_for_backward(means3d, scales, rots, opacities, colors, view, proj, tanfov, bg)
+        ctx.shapes = tuple(t.shape for t in (means3d, scales, rots, opacities, colors))
+        return fwd["color"]
+
+    @staticmethod
+    def backward(ctx, grad_color):
+        means3d, scales, rots, opacities, colors, view, proj, tanfov, bg = ctx.saved_tensors
+        height, width, vps, activate, hwc, smod = ctx.args
+        g = splat_backward(ctx.fwd, grad_color, means3d, scales, rots, opacities, colors, view, proj, tanfov, bg,
+                           height, width, views_per_set=vps, activate=activate, hwc=hwc, scale_modifier=smod)
+        ctx.fwd = None
+        outs = [g[k].reshape(s) for k, s in zip(("means3d", "scales", "rots", "opacities", "colors"), ctx.shapes)]
+        return (*outs, None, None, None, None, None, None, None, None, None, None, None)
+
+
+def splat_render(means3d, scales, rots, opacities, colors, view, proj, tanfov, bg, height, width, *,
+                 views_per_set=1, activate=False, hwc=False, clamp01=False, scale_modifier=1.0) -> torch.Tensor:
+    """Autograd-aware colour output of the splat ([F,3,H,W] or [F,H,W,3])."""
+    return SplatFunction.apply(means3d, scales, rots, opacities, colors, view, proj, tanfov, bg, int(height), int(width),
+                               int(views_per_set), bool(activate), bool(hwc), bool(clamp01), float(scale_modifier))

@@ -151,6 +151,32 @@ int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *
                      float *out_color, float *final_T, int32_t *n_contrib, float *out_invdepth,
                      uint32_t *work_counter, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Stage 4 backward (diff_gaussian_rasterization's _RasterizeGaussians.backward, reached in the reference
+ * through autograd from renderer.py:555-568).  Needs the forward's geom, tile_start,
+ * point_list, final_T and n_contrib.
+ *
+ * amav_splat_blend_backward: dL/d(colour output) -> per-(frame, Gaussian) screen-space sums
+ *   dL_dcolor [F,3,H,W] (hwc=0) or [F,H,W,3] (hwc=1): gradient w.r.t. the blend's colour output (the [0,1] clamp
+ *             of renderer.py:568 is the identity for colours and backgrounds inside [0,1])
+ *   dsum      [F,N,12] fp32, MUST be zeroed by the caller, 16-byte aligned:
+ *             0,1 dL/dmean2D (x 0.5*W, 0.5*H as upstream), 2..4 dL/dconic (A, B, C; B holds half the true
+ *             derivative, upstream's convention), 5 dL/dopacity, 6..8 dL/drgb, 9..11 unused
+ *   work_counter [1] uint32: MUST be zeroed by the caller.
+ * amav_splat_preprocess_backward: sums -> gradients of the rasteriser inputs, through render_one's activations when
+ *   d->activate (renderer.py:532-533,547), summed over the views_per_set views that share a Gaussian set.
+ *   d_means3d/d_scales/d_colors [G,N,3], d_rots [G,N,4] (16-byte aligned), d_opacities [G,N], G = F/views_per_set.
+ */
+int amav_splat_blend_backward(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
+                              const int32_t *point_list, int64_t capacity, const float *bg, int hwc,
+                              const float *final_T, const int32_t *n_contrib, const float *dL_dcolor,
+                              float *dsum, uint32_t *work_counter, void *stream);
+int amav_splat_preprocess_backward(const AmavSplatDims *d, const float *means3d, const float *scales,
+                                   const float *rots, const float *opacities, const float *colors,
+                                   const float *view, const float *proj, const float *tanfov,
+                                   const float *geom, const float *dsum, float *d_means3d, float *d_scales,
+                                   float *d_rots, float *d_opacities, float *d_colors, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
