@@ -20,6 +20,7 @@ SOURCES = [
     ("splat_blend_bwd.cu", ["-fmad=false"]),
     ("splat_preprocess_bwd.cu", []),
     ("triplane.cu", []),
+    ("triplane_bwd.cu", []),
     ("lbs.cu", []),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

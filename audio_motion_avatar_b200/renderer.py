@@ -23,7 +23,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib, stages, synthetic
-from .splat import SplatWorkspace, splat_forward
+from .splat import SplatWorkspace, splat_forward, splat_render
 
 SUBDEVIDE_VERTS = {0: 10000, 1: 30000, 2: 30000}      # renderer.py:14-18 (sic)
 SCALE_BIAS = 3.9                                        # renderer.py:428
@@ -119,6 +119,10 @@ def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug,
         opacity = torch.full_like(opacity, 0.1)
         color = color.clamp(0.0, 1.0)
         activate = False
+    if torch.is_grad_enabled() and any(t.requires_grad for t in (xyz, rot, scale, opacity, color)):
+        # training: autograd node with its own buffers (the forward's lists and per-pixel state feed the backward)
+        return splat_render(xyz, scale, rot, opacity, color, view, full, tanfov, bg, height, width,
+                            views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=True)
     ws = _workspace(dev)
 
     def run(sync_free):
@@ -325,6 +329,8 @@ class Renderer(nn.Module):
         """Stages 1+2 for [F,C,3*R*R] tokens and [F,N,3] posed sites -> the ``gaussians`` dict."""
         C, R = int(self.cfg.triplane_feature_dim), int(self.cfg.triplane_resolution)
         W, b = self._decoder_wb()
+        if torch.is_grad_enabled() and any(t.requires_grad for t in (triplane_features, points, transl, W, b)):
+            return stages.decode_gaussians_autograd(triplane_features, points, transl, W, b, C, R, float(self.cfg.radius))
         proj = stages.triplane_project(triplane_features, W, C, R)
         return stages.sample_decode(proj, points, transl, W, b, C, R, float(self.cfg.radius))
 

@@ -140,3 +140,77 @@ def sample_decode(proj: torch.Tensor, points: torch.Tensor, transl: torch.Tensor
          ptr(_f32c(transl.reshape(Fr, 3))), ptr(_f32c(weight)), ptr(_f32c(bias)), ptr(xyz), ptr(scale), ptr(rot),
          ptr(opacity), ptr(color), stream_ptr())
     return {"xyz": xyz, "scale": scale, "rot": rot, "opacity": opacity, "color": color, "shs": color}
+
+
+# ------------------------------------------------------------------------------------------------
+# backward of stages 1+2 and the autograd node the Renderer uses in training
+# ------------------------------------------------------------------------------------------------
+def sample_decode_backward(proj, points, weight, bias, grads: Dict[str, Optional[torch.Tensor]], C: int, R: int,
+                           radius: float, want_points: bool = True):
+    """grads: dL/d{xyz,scale,rot,opacity,color} ([F,N,k] or None).  Returns (d_proj [F,3,R*R,16], d_points [F,N,3] or
+    None, d_transl [F,3], d_wb [14,4])."""
+    Fr, N = int(points.shape[0]), int(points.shape[1])
+    dev = points.device
+    d_proj = torch.zeros(Fr, 3, R * R, 16, device=dev)
+    d_points = torch.empty(Fr, N, 3, device=dev) if want_points else None
+    d_transl = torch.zeros(Fr, 3, device=dev)
+    d_wb = torch.zeros(14, 4, device=dev)
+    g = lambda k: None if grads.get(k) is None else _f32c(grads[k])
+    gx, gs, gr, go, gc = g("xyz"), g("scale"), g("rot"), g("opacity"), g("color")
+    call("amav_sample_decode_backward", Fr, N, C, R, float(radius), ptr(proj), ptr(_f32c(points)), ptr(_f32c(weight)),
+         ptr(_f32c(bias)), ptr(gx), ptr(gs), ptr(gr), ptr(go), ptr(gc), ptr(d_proj), ptr(d_points), ptr(d_transl),
+         ptr(d_wb), stream_ptr())
+    return d_proj, d_points, d_transl, d_wb
+
+
+def triplane_project_backward(d_proj, tokens, weight, C: int, R: int, want_tokens: bool = True, want_weight: bool = True):
+    """d_proj [F,3,R*R,16] -> (d_tokens [F,C,3*R*R] or None, d_weight [14,3+3C] feature columns or None)."""
+    Fr = int(d_proj.shape[0])
+    dev = d_proj.device
+    d_tokens = torch.empty(Fr, C, 3 * R * R, device=dev) if want_tokens else None
+    d_weight = torch.zeros(14, 3 + 3 * C, device=dev) if want_weight else None
+    tok_ptr, fstride = None, C * 3 * R * R
+    if want_weight:
+        if tokens.stride(2) != 1 or tokens.stride(1) != 3 * R * R:
+            tokens = tokens.contiguous()
+        tok_ptr = ctypes_ptr(tokens)
+        fstride = int(tokens.stride(0)) if Fr > 1 else C * 3 * R * R
+    call("amav_triplane_project_backward", Fr, C, R, ptr(d_proj), tok_ptr, fstride, ptr(_f32c(weight)), ptr(d_tokens),
+         C * 3 * R * R, 0, ptr(d_weight), stream_ptr())
+    return d_tokens, d_weight
+
+
+class DecodeFunction(torch.autograd.Function):
+    """tokens [F,C,3R^2], points [F,N,3], transl [F,3], weight [14,3+3C], bias [14] -> (xyz, scale, rot, opacity, color):
+    project-then-sample forward, and its hand-written backward (no [F,N,1536] feature tensor in either direction)."""
+
+    @staticmethod
+    def forward(ctx, tokens, points, transl, weight, bias, C, R, radius):
+        proj = triplane_project(tokens, weight.detach(), C, R)
+        g = sample_decode(proj, points, transl, weight.detach(), bias.detach(), C, R, radius)
+        ctx.save_for_backward(tokens, points, weight, bias, proj)
+        ctx.dims = (C, R, radius)
+        return g["xyz"], g["scale"], g["rot"], g["opacity"], g["color"]
+
+    @staticmethod
+    def backward(ctx, g_xyz, g_scale, g_rot, g_opacity, g_color):
+        tokens, points, weight, bias, proj = ctx.saved_tensors
+        C, R, radius = ctx.dims
+        need_tok, need_pts, need_tr, need_w, need_b = ctx.needs_input_grad[:5]
+        d_proj, d_points, d_transl, d_wb = sample_decode_backward(
+            proj, points, weight, bias, {"xyz": g_xyz, "scale": g_scale, "rot": g_rot, "opacity": g_opacity, "color": g_color},
+            C, R, radius, want_points=need_pts)
+        d_tokens = d_weight = None
+        if need_tok or need_w:
+            d_tokens, d_weight = triplane_project_backward(d_proj, tokens, weight, C, R, want_tokens=need_tok, want_weight=need_w)
+            if d_weight is not None:
+                d_weight[:, :3] = d_wb[:, :3]
+            if d_tokens is not None and d_tokens.shape != tokens.shape:
+                d_tokens = d_tokens.reshape(tokens.shape)
+        return (d_tokens, d_points, d_transl.reshape(-1, 3) if need_tr else None, d_weight,
+                d_wb[:, 3].contiguous() if need_b else None, None, None, None)
+
+
+def decode_gaussians_autograd(tokens, points, transl, weight, bias, C: int, R: int, radius: float) -> Dict[str, torch.Tensor]:
+    xyz, scale, rot, opacity, color = DecodeFunction.apply(tokens, points, transl, weight, bias, int(C), int(R), float(radius))
+    return {"xyz": xyz, "scale": scale, "rot": rot, "opacity": opacity, "color": color, "shs": color}

@@ -177,6 +177,29 @@ int amav_splat_preprocess_backward(const AmavSplatDims *d, const float *means3d,
                                    const float *geom, const float *dsum, float *d_means3d, float *d_scales,
                                    float *d_rots, float *d_opacities, float *d_colors, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Stages 1+2 backward (autograd of renderer.py:292-317 grid_sample, :165-171 the five Linear heads and
+ * :319-346 construct_gaussians in the reference).
+ *
+ * amav_sample_decode_backward: gradients w.r.t. the `gaussians` dict entries (g_*: [F,N,k], each may be NULL = 0)
+ *   -> d_proj   [F,3,R*R,16], MUST be zeroed by the caller: gradient of the projected planes (float4 reductions)
+ *      d_points [F,N,3] (may be NULL): direct term + xyz columns of the heads + bilinear position derivative
+ *                (zero outside the clamp of renderer.py:298)
+ *      d_transl [F,3] (may be NULL), MUST be zeroed by the caller
+ *      d_wb     [14,4], MUST be zeroed by the caller: dL/dW[:, 0:3] in columns 0..2 and dL/dbias in column 3
+ * amav_triplane_project_backward:
+ *      d_tokens [F,C,3*R*R] (frame stride d_token_frame_stride; may be NULL) = W_feat^T . d_proj, overwritten, or
+ *                added to when accumulate_tokens != 0
+ *      d_weight [14,3+3C] (may be NULL; then tokens may be NULL): feature columns 3.. are ADDED to (zero it first)
+ */
+int amav_sample_decode_backward(int F, int N, int C, int R, float radius, const float *proj, const float *points,
+                                const float *weight, const float *bias, const float *g_xyz, const float *g_scale,
+                                const float *g_rot, const float *g_opacity, const float *g_color, float *d_proj,
+                                float *d_points, float *d_transl, float *d_wb, void *stream);
+int amav_triplane_project_backward(int F, int C, int R, const float *d_proj, const float *tokens,
+                                   int64_t token_frame_stride, const float *weight, float *d_tokens,
+                                   int64_t d_token_frame_stride, int accumulate_tokens, float *d_weight, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -329,7 +329,7 @@ def sample_from_triplane_torch(triplane: torch.Tensor, points: torch.Tensor, rad
 
 
 def reference_frames(model, weights, tokens, params, K, E, height, width, channels, res, radius=1.4,
-                     level_edges=None, site_idx=None, bg=(1.0, 1.0, 1.0)):
+                     level_edges=None, site_idx=None, bg=(1.0, 1.0, 1.0), differentiable=False):
     """The reference's Renderer.forward (renderer.py:73-204) for F frames on the CPU: LBS -> (subdivide + subset)
     -> grid_sample twice (the reference samples at initial and refined points, renderer.py:136,158; the refiner
     offset is exactly zero at init) -> five Linear heads -> construct_gaussians -> per-frame render_one.
@@ -344,7 +344,8 @@ def reference_frames(model, weights, tokens, params, K, E, height, width, channe
     sample_from_triplane_torch(tri, pts, radius)                                               # renderer.py:136
     feats = sample_from_triplane_torch(tri, pts, radius)                                       # renderer.py:158
     g = construct_gaussians(decode_heads(pts, feats, weights), pts, params["transl"])
-    imgs = [render_one({k: v[f] for k, v in g.items()}, K[f], E[f], height, width, bg).permute(1, 2, 0) for f in range(Fr)]
+    one = render_one_autograd if differentiable else render_one      # autograd through the C rasteriser's backward
+    imgs = [one({k: v[f] for k, v in g.items()}, K[f], E[f], height, width, bg).permute(1, 2, 0) for f in range(Fr)]
     return torch.stack(imgs), g
 
 
