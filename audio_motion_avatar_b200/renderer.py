@@ -278,13 +278,13 @@ class Renderer(nn.Module):
     def get_smpl_vertices(self, smpl_params):
         """renderer.py:245-290: posed vertices (no transl), optionally densified + subset -> [B*T, N, 3]."""
         full, shape = self.smplx_model.full_pose(smpl_params)
-        verts = stages.lbs_forward(self.smplx_model, full, shape)
+        verts = stages.lbs_vertices(self.smplx_model, full, shape)
         if getattr(self.cfg, "densify_smplx_verts", False):
             idx = self._fixed_idx
             if idx is None:
                 idx = torch.randperm(int(self._dense_par.shape[0]))[:self.num_verts].to(self._device)
-            verts = stages.densify_gather(verts, self._dense_par.index_select(0, idx).contiguous(),
-                                          self._dense_wgt.index_select(0, idx).contiguous())
+            verts = stages.densify_sites(verts, self._dense_par.index_select(0, idx).contiguous(),
+                                         self._dense_wgt.index_select(0, idx).contiguous())
         return verts
 
     def _decoder_wb(self):

@@ -214,3 +214,64 @@ class DecodeFunction(torch.autograd.Function):
 def decode_gaussians_autograd(tokens, points, transl, weight, bias, C: int, R: int, radius: float) -> Dict[str, torch.Tensor]:
     xyz, scale, rot, opacity, color = DecodeFunction.apply(tokens, points, transl, weight, bias, int(C), int(R), float(radius))
     return {"xyz": xyz, "scale": scale, "rot": rot, "opacity": opacity, "color": color, "shs": color}
+
+
+# ------------------------------------------------------------------------------------------------
+# backward of stage 3 (LBS + densify) as autograd nodes
+# ------------------------------------------------------------------------------------------------
+class LbsFunction(torch.autograd.Function):
+    """(full_pose [F,J*3], shape_comp [F,S]) -> posed vertices [F,V,3]; gradients by amav_lbs_backward."""
+
+    @staticmethod
+    def forward(ctx, body, full_pose, shape_comp):
+        verts, aux = lbs_forward(body, full_pose, shape_comp, return_aux=True)
+        ctx.body = body
+        ctx.save_for_backward(full_pose, shape_comp, aux["A"], aux["v_posed"])
+        return verts
+
+    @staticmethod
+    def backward(ctx, d_verts):
+        body = ctx.body
+        full_pose, shape_comp, A, v_posed = ctx.saved_tensors
+        Fr, dev = int(full_pose.shape[0]), body.device
+        d_v_posed = torch.empty(Fr, body.V, 3, device=dev)
+        d_A = torch.zeros(Fr, body.J, 12, device=dev)
+        d_pf = torch.zeros(Fr, (body.J - 1) * 9, device=dev)
+        d_pose = torch.empty(Fr, body.J * 3, device=dev)
+        d_shape = torch.zeros(Fr, body.S, device=dev)
+        call("amav_lbs_backward", Fr, body.V, body.J, body.S, ptr(_f32c(full_pose)), ptr(_f32c(shape_comp)),
+             ptr(body.shapedirs), ptr(body.posedirs), ptr(body.parents), ptr(body.J_template), ptr(body.J_dirs),
+             ptr(body.weights_T), ptr(A), ptr(v_posed), ptr(_f32c(d_verts)), ptr(d_v_posed), ptr(d_A), ptr(d_pf),
+             ptr(d_pose), ptr(d_shape), stream_ptr())
+        return None, d_pose, d_shape
+
+
+class DensifyFunction(torch.autograd.Function):
+    """verts [F,V,3] -> sites [F,N,3] through the fixed (parents, weights) table."""
+
+    @staticmethod
+    def forward(ctx, verts, par, wgt):
+        ctx.save_for_backward(par, wgt)
+        ctx.V = int(verts.shape[1])
+        return densify_gather(verts, par, wgt)
+
+    @staticmethod
+    def backward(ctx, d_sites):
+        par, wgt = ctx.saved_tensors
+        Fr, N, P = int(d_sites.shape[0]), int(par.shape[0]), int(par.shape[1])
+        d_verts = torch.zeros(Fr, ctx.V, 3, device=d_sites.device)
+        call("amav_densify_gather_backward", Fr, ctx.V, N, P, ptr(_f32c(d_sites)), ptr(par), ptr(wgt), ptr(d_verts), stream_ptr())
+        return d_verts, None, None
+
+
+def lbs_vertices(body: BodyModel, full_pose: torch.Tensor, shape_comp: torch.Tensor) -> torch.Tensor:
+    """Autograd-aware LBS: the plain forward when nothing requires a gradient."""
+    if torch.is_grad_enabled() and (full_pose.requires_grad or shape_comp.requires_grad):
+        return LbsFunction.apply(body, full_pose, shape_comp)
+    return lbs_forward(body, full_pose, shape_comp)
+
+
+def densify_sites(verts: torch.Tensor, par: torch.Tensor, wgt: torch.Tensor) -> torch.Tensor:
+    if torch.is_grad_enabled() and verts.requires_grad:
+        return DensifyFunction.apply(verts, par, wgt)
+    return densify_gather(verts, par, wgt)

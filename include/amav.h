@@ -200,6 +200,23 @@ int amav_triplane_project_backward(int F, int C, int R, const float *d_proj, con
                                    int64_t token_frame_stride, const float *weight, float *d_tokens,
                                    int64_t d_token_frame_stride, int accumulate_tokens, float *d_weight, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Stage 3 backward (autograd of smplx.lbs.lbs and of the densify gather in the reference, renderer.py:261-288;
+ * exercised when the SMPL-X parameters are predicted, i.e. stage-2 training).
+ *
+ * amav_densify_gather_backward: d_verts [F,V,3] (MUST be zeroed by the caller) += wgt * d_sites [F,N,3].
+ * amav_lbs_backward: d_verts [F,V,3] -> d_full_pose [F,J*3] (overwritten), d_shape [F,S] (MUST be zeroed).
+ *   A, v_posed: the forward's work buffers (amav_lbs_forward); d_v_posed [F,V,3] scratch;
+ *   d_A [F,J,12] and d_pose_feature [F,(J-1)*9] scratch, MUST be zeroed by the caller.
+ */
+int amav_densify_gather_backward(int F, int V, int N, int P, const float *d_sites, const int32_t *par,
+                                 const float *wgt, float *d_verts, void *stream);
+int amav_lbs_backward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
+                      const float *shapedirs, const float *posedirs, const int32_t *parents,
+                      const float *J_template, const float *J_dirs, const float *weights_T, const float *A,
+                      const float *v_posed, const float *d_verts, float *d_v_posed, float *d_A,
+                      float *d_pose_feature, float *d_full_pose, float *d_shape, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

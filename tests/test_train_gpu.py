@@ -121,3 +121,68 @@ def test_renderer_training_step_gradients():
         ew = _rel(layer.weight.grad.cpu(), w_r[f"{n}_layer.weight"].grad)
         eb = _rel(layer.bias.grad.cpu(), w_r[f"{n}_layer.bias"].grad)
         assert ew <= 2e-3 and eb <= 2e-3, (n, ew, eb)
+
+
+POSE_KEYS = ("global_orient", "body_pose", "jaw_pose", "leye_pose", "reye_pose", "left_hand_pose", "right_hand_pose",
+             "betas", "expression")
+
+
+def test_lbs_and_densify_backward_match_autograd():
+    """d(verts)/d(pose, betas, expression) through amav_lbs_backward and the densify scatter vs torch autograd of the
+    oracle's smplx restatement (19 frames: a ragged 16-frame group)."""
+    from audio_motion_avatar_b200.stages import BodyModel, densify_sites, lbs_vertices
+    model = S.make_body_model(seed=0)
+    body = BodyModel(model, "cuda:0")
+    Fr = 19
+    params = S.make_pose_sequence(1, Fr, seed=4)
+    flat = {k: v.reshape(Fr, *v.shape[2:]) for k, v in params.items()}
+    V = model["v_template"].shape[0]
+    par, wgt = S.densify_table(V, model["faces"].numpy(), 1)
+    idx = torch.randperm(par.shape[0], generator=torch.Generator().manual_seed(1))[:20000]
+    par_t, wgt_t = torch.from_numpy(par)[idx], torch.from_numpy(wgt)[idx]
+    up = torch.randn(Fr, 20000, 3, generator=torch.Generator().manual_seed(2))
+    # oracle
+    leaves = {k: flat[k].clone().requires_grad_(True) for k in POSE_KEYS}
+    verts = O.lbs_vertices({**flat, **leaves}, model)
+    sites = (verts[:, par_t.long()] * wgt_t[None, :, :, None]).sum(2)
+    (sites * up).sum().backward()
+    # CUDA
+    d = torch.device("cuda:0")
+    dl = {k: flat[k].clone().to(d).requires_grad_(True) for k in POSE_KEYS}
+    full, shape = body.full_pose(dl)
+    out = densify_sites(lbs_vertices(body, full, shape), par_t.to(d).contiguous(), wgt_t.to(d).contiguous())
+    assert (out.detach().cpu() - sites.detach()).abs().max().item() < 5e-5
+    (out * up.to(d)).sum().backward()
+    torch.cuda.synchronize()
+    for k in POSE_KEYS:
+        e = _rel(dl[k].grad.cpu(), leaves[k].grad)
+        assert e <= 1e-3, (k, e)
+
+
+def test_stage2_pose_gradients_end_to_end():
+    """Image loss -> splat -> decode (position derivative of the triplane query) -> LBS -> pose parameters and transl:
+    the gradient path of stage-2 training, where the SMPL-X parameters are predicted (triplane_audio_net.py:269)."""
+    from audio_motion_avatar_b200.renderer import Renderer
+    H, W, C, R, T = 64, 48, 64, 16, 2
+    model = S.make_body_model(seed=0)
+    w = S.make_decoder_weights(C, seed=0)
+    tokens = S.make_triplane_tokens(T, C, R, seed=0)
+    params = S.make_pose_sequence(1, T, seed=0)
+    cams = S.make_cameras(1, T, H, W)
+    gimg = torch.randn(1, T, H, W, 3, generator=torch.Generator().manual_seed(3))
+    keys = POSE_KEYS + ("transl",)
+    flat = {k: v.reshape(T, *v.shape[2:]) for k, v in params.items()}
+    leaves = {k: flat[k].clone().requires_grad_(True) for k in keys}
+    ref, _ = O.reference_frames(model, w, tokens[0], {**flat, **leaves}, cams["intrinsic"][0], cams["extrinsic"][0], H, W, C, R,
+                                differentiable=True)
+    (ref * gimg[0]).sum().backward()
+    d = torch.device("cuda:0")
+    r = Renderer(_cfg(H, W, C, R), body_model=model)
+    r.gaussian_decoder.load_state_dict(w)
+    dl = {k: params[k].clone().to(d).requires_grad_(True) for k in keys}
+    img, _ = r(tokens.to(d), {k: v.to(d) for k, v in cams.items()}, None, {**{k: v.to(d) for k, v in params.items()}, **dl})
+    (img * gimg.to(d)).sum().backward()
+    torch.cuda.synchronize()
+    for k in keys:
+        e = _rel(dl[k].grad.cpu().reshape(leaves[k].grad.shape), leaves[k].grad)
+        assert e <= 5e-3, (k, e)
