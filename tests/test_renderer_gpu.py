@@ -161,3 +161,46 @@ def test_camera_matrices_match_reference_golden(golden_dir):
         assert np.abs(v[0].cpu().numpy() - g[f"view_{i}"]).max() <= 1e-5 * max(1.0, np.abs(g[f"view_{i}"]).max())
         assert np.abs(f[0].cpu().numpy() - g[f"full_{i}"]).max() <= 1e-5 * max(1.0, np.abs(g[f"full_{i}"]).max())
         assert abs(float(t[0, 0]) - float(g[f"tanfovx_{i}"])) <= 1e-6 and abs(float(t[0, 1]) - float(g[f"tanfovy_{i}"])) <= 1e-6
+
+
+def test_diff_gaussian_rasterization_shim_runs_reference_render_one():
+    """The reference's own render_one body (renderer.py:516-568: settings, activations, rasterizer call, clamp) on top
+    of the import-compatible shim equals this repo's render_one, forward and backward."""
+    from audio_motion_avatar_b200 import compat
+    from audio_motion_avatar_b200.renderer import camera_matrices, render_one, SCALE_BIAS, OPACITY_BIAS
+    compat.install_diff_gaussian_rasterization()
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from tests.helpers import random_scene
+    H, W, N = 96, 80, 3000
+    sc = random_scene(N, W, H, seed=4, frames=1)
+    d = torch.device("cuda:0")
+    raw = {"xyz": sc["means"], "rot": sc["rots"], "scale": torch.log(sc["scales"]) + 3.9,
+           "opacity": torch.logit(sc["opac"].clamp(0.02, 0.98)), "color": sc["col"]}
+    K, E = sc["K"][0].to(d), sc["E"][0].to(d)
+    args = SimpleNamespace(image_size=(H, W), rgb=True, sh_degree=3)
+    a = {k: v.clone().to(d).requires_grad_(True) for k, v in raw.items()}
+    b = {k: v.clone().to(d).requires_grad_(True) for k, v in raw.items()}
+    ours = render_one(a["xyz"], a["rot"], a["scale"], a["opacity"], a["color"], K, E, args)
+    # --- the reference's call sequence ---
+    view, full, tan = camera_matrices(K[None], E[None], H, W)
+    settings = GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=float(tan[0, 0]), tanfovy=float(tan[0, 1]),
+                                             bg=torch.tensor([1, 1, 1], dtype=torch.float32, device="cuda"), scale_modifier=1.0,
+                                             viewmatrix=view[0], projmatrix=full[0], sh_degree=3,
+                                             campos=view[0].inverse()[3, :3], prefiltered=False, debug=False, antialiasing=False)
+    scales = torch.min(torch.exp(b["scale"] - SCALE_BIAS), torch.tensor(0.1, device=d))
+    opacities = torch.sigmoid(b["opacity"] - OPACITY_BIAS)
+    colors_precomp = torch.clamp(b["color"], 0.0, 1.0)
+    screenspace_points = torch.zeros_like(b["xyz"], requires_grad=True) + 0
+    rendered, radii, inv_depth = GaussianRasterizer(raster_settings=settings)(
+        means3D=b["xyz"], means2D=screenspace_points, shs=None, colors_precomp=colors_precomp, opacities=opacities,
+        scales=scales, rotations=b["rot"], cov3D_precomp=None)
+    rendered = rendered.clamp(0, 1)
+    assert rendered.shape == (3, H, W) and radii.shape == (N,) and radii.dtype == torch.int32 and inv_depth.shape == (1, H, W)
+    assert (radii > 0).sum() > N // 2
+    assert (ours - rendered).abs().max().item() <= 2e-6          # torch's exp/sigmoid vs the fused activations
+    gimg = torch.randn(3, H, W, device=d, generator=torch.Generator(device=d).manual_seed(0))
+    (ours * gimg).sum().backward()
+    (rendered * gimg).sum().backward()
+    for k in raw:
+        ga, gb = a[k].grad, b[k].grad
+        assert (ga - gb).abs().max().item() <= 1e-3 * gb.abs().max().item() + 1e-7, k
