@@ -55,3 +55,30 @@ def shard_inputs(tokens: torch.Tensor, cams: dict, params: dict, rank: int, worl
     s, e = frame_shard(T, rank, world)
     cut = lambda t: t[:, s:e]
     return cut(tokens), {k: cut(v) for k, v in cams.items()}, {k: cut(v) for k, v in params.items()}
+
+
+# ------------------------------------------------------------------------------------------------
+# training (SURVEY.md 8e, config c4): the (subject, view) render jobs are split over ranks by VIEW; every rank decodes
+# the same subjects' Gaussians, renders its own views, and the gradients that the views share -- dL/dtriplane tokens
+# and the decoder's dL/dW, dL/db -- are summed with ONE all-reduce over a flat bucket.
+# ------------------------------------------------------------------------------------------------
+def view_shard(num_views: int, rank: int, world: int) -> Tuple[int, int]:
+    """[start, stop) of the views rank renders (same rule as frame_shard)."""
+    return frame_shard(num_views, rank, world)
+
+
+def allreduce_gradients(tensors: List[Optional[torch.Tensor]], group=None, average: bool = False) -> None:
+    """Sum (or average) the given gradient tensors over the ranks in place: one flat bucket, one collective.
+    ``None`` entries are skipped (all ranks must pass the same structure)."""
+    live = [t for t in tensors if t is not None]
+    if not live or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    flat = torch.cat([t.reshape(-1) for t in live])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    if average:
+        flat /= dist.get_world_size(group)
+    off = 0
+    for t in live:
+        n = t.numel()
+        t.copy_(flat[off:off + n].view_as(t))
+        off += n

@@ -50,6 +50,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
+    ap.add_argument("--workload", default="sequence", choices=["sequence", "train"],
+                    help="sequence = BASELINE.json configs[1] (the headline metric); train = configs[3], a secondary line")
+    ap.add_argument("--subjects", type=int, default=4)
+    ap.add_argument("--views", type=int, default=4)
     return ap.parse_args()
 
 
@@ -144,6 +148,20 @@ def stage_bytes(name, Fr, N, V, J, S, P, H, W, D):
         return Fr * N * (8 + 4) + D * (8 + 8 + 4) + Fr * tiles * 8
     if name == "amav_splat_blend":
         return D * (4 + 48) + Fr * H * W * 12 + Fr * tiles * 4
+    # backward stages (Fr = frames the stage sees; for decode / LBS stages that is the number of Gaussian sets)
+    if name == "amav_splat_blend_backward":
+        return D * (4 + 48) + Fr * H * W * (12 + 8) + Fr * N * 48 + Fr * tiles * 4
+    if name == "amav_splat_preprocess_backward":
+        return Fr * N * (16 + 36) + (Fr // max(P, 1)) * N * (56 + 56)          # P = views per set here
+    if name == "amav_sample_decode_backward":
+        return Fr * (N * (12 + 56 + 12) + 2 * 3 * R2 * 64)
+    if name == "amav_triplane_project_backward":
+        return Fr * (2 * 3 * C * R2 * 4 + 2 * 3 * R2 * 64) + 14 * (3 * C + 3) * 4
+    if name == "amav_lbs_backward":
+        const = (J - 1) * 9 * 3 * V * 4 + V * 3 * S * 4 + J * V * 4
+        return const + Fr * (4 * V * 12 + J * 48 * 2)
+    if name == "amav_densify_gather_backward":
+        return N * P * 8 + Fr * (V * 12 + N * 12)
     return 0
 
 
@@ -334,10 +352,111 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_train(args):
+    """BASELINE.json configs[3]: one training step = `subjects` Gaussian sets (each its own triplane and pose) decoded
+    once and rendered from `views` cameras, 100k Gaussians, 512x512, L1 image loss, full backward through the splat,
+    the decode / triplane query and LBS, SGD step on the decoder.  N > 1: views are sharded over ranks (each rank
+    renders `views` views of the same subjects: weak scaling) and dL/dtokens + decoder gradients are all-reduced."""
+    import torch.distributed as dist
+    from audio_motion_avatar_b200 import _lib, synthetic as S
+    from audio_motion_avatar_b200.renderer import Renderer, render_multi_view
+    from audio_motion_avatar_b200.shard import allreduce_gradients
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (there is no CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    warmup, steps = max(3, args.warmup), max(1, args.steps)
+    B, Tv, N = args.subjects, args.views, args.gaussians
+    size = args.size if args.size != SIZE else 512
+    model = S.make_body_model(seed=0)
+    r = Renderer(make_cfg(size, N, f"cuda:{local}"), body_model=model)
+    r.gaussian_decoder.load_state_dict(S.make_decoder_weights(C, seed=0))
+    if N != 10475:
+        r.fix_site_subset(seed=0)
+    g = torch.Generator(device=dev).manual_seed(0)                                 # same subjects on every rank
+    tokens = torch.randn(B, 1, C, 3 * R * R, device=dev, generator=g).requires_grad_(True)
+    params = {k: v.reshape(B, 1, *v.shape[2:]).to(dev) for k, v in S.make_pose_sequence(1, B, seed=0).items()}
+    params["transl"] = torch.tensor([0.0, 0.35, 0.0], device=dev).expand(B, 1, 3).contiguous()   # body at the orbit centre
+    pose_leaves = {k: params[k].clone().requires_grad_(True) for k in ("global_orient", "body_pose", "betas", "expression", "transl")}
+    params = {**params, **pose_leaves}
+    cams = S.make_cameras(B, Tv, size, size, orbit=True)                              # 4 cameras on a 2.4 m circle (SURVEY 8d)
+    cams = {k: v.to(dev) for k, v in cams.items()}
+    target = torch.rand(B, Tv, size, size, 3, device=dev, generator=g)
+    opt = torch.optim.SGD(r.gaussian_decoder.parameters(), lr=1e-4)
+    leaves = [tokens] + list(pose_leaves.values())
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        for t in leaves:
+            t.grad = None
+        first = {k: v[:, :1] for k, v in cams.items()}
+        img, gs = r(tokens, first, None, params)                                     # decode + view 0
+        loss = (img - target[:, :1]).abs().mean()
+        if Tv > 1:
+            mv = render_multi_view(gs, cams["intrinsic"][:, 1:], cams["extrinsic"][:, 1:], r.cfg)
+            loss = (loss + (mv - target[:, 1:]).abs().mean() * (Tv - 1)) / Tv
+        loss.backward()
+        if world > 1:
+            allreduce_gradients([tokens.grad] + [p.grad for p in r.gaussian_decoder.parameters()])
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        step()
+    barrier()
+    launches0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks, _lib.StageTimer() as timer:
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            loss = step()
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = (_lib.launch_count() - launches0) // steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / steps
+    stages_ms = {k: (v[0] / steps, v[1] // steps) for k, v in timer.summary().items()}
+    peak, peak_src = peaks()
+    body = r.smplx_model
+    P = int(r._dense_par.shape[1]) if r._dense_par is not None else 1
+    per_stage = {k: {"ms": round(v[0], 4), "calls": v[1]} for k, v in stages_ms.items()}
+    line = {"metric": "training renders/sec (fwd+bwd) @100k Gaussians 512^2", "value": world * B * Tv / (ms_per_step * 1e-3),
+            "unit": "(subject,view) renders/s", "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"training step: {B} subjects x {Tv} views per rank, {N} Gaussians, {size}x{size}, forward + "
+                                   "backward through splat, decode/triplane query and LBS, SGD on the decoder "
+                                   "(BASELINE.json configs[3])",
+                       "parallelism": f"view-sharded x{world}" + ("" if world == 1 else " + NCCL all-reduce of dL/dtokens and decoder grads")},
+            "clocks": clocks.summary(), "gpu_launches": int(launches), "loss": float(loss.item()),
+            "stages": per_stage, "peak_hbm_gbs": peak, "peak_source": peak_src,
+            "body": {"V": body.V, "J": body.J, "P": P}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "train":
+        run_train(args)
     else:
         run_ours(args)
 

@@ -61,3 +61,42 @@ def test_gather_frames_gloo(world, F):
         p.join(120)
         assert p.exitcode == 0
     assert q.get(timeout=10) is True
+
+
+def _grad_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from audio_motion_avatar_b200.shard import allreduce_gradients, view_shard
+        # a "loss" that is a sum over views of w * view_weight: rank r owns views [s, e)
+        views = 5
+        s, e = view_shard(views, rank, world)
+        w = torch.arange(6, dtype=torch.float32).reshape(2, 3).requires_grad_(True)
+        b = torch.ones(4, requires_grad=True)
+        loss = sum((w * (v + 1)).sum() + (b * (v + 1) ** 2).sum() for v in range(s, e))
+        if e > s:
+            loss.backward()
+        else:
+            w.grad, b.grad = torch.zeros_like(w), torch.zeros_like(b)
+        allreduce_gradients([w.grad, None, b.grad])
+        ok = torch.allclose(w.grad, torch.full((2, 3), float(sum(v + 1 for v in range(views))))) and \
+            torch.allclose(b.grad, torch.full((4,), float(sum((v + 1) ** 2 for v in range(views)))))
+        q.put(bool(ok))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_allreduce_gradients_view_sharded_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    world = 2
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_grad_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=10) is True and q.get(timeout=10) is True
