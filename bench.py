@@ -238,6 +238,7 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.pop("NCCL_DEBUG", None)          # NCCL prints its version banner on stdout; stdout carries the JSON line
         dist.init_process_group("nccl", device_id=dev)
     warmup = max(3, args.warmup)
     steps = max(1, args.steps)
@@ -369,6 +370,7 @@ def run_train(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.pop("NCCL_DEBUG", None)          # NCCL prints its version banner on stdout; stdout carries the JSON line
         dist.init_process_group("nccl", device_id=dev)
     warmup, steps = max(3, args.warmup), max(1, args.steps)
     B, Tv, N = args.subjects, args.views, args.gaussians
