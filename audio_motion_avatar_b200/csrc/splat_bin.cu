@@ -189,17 +189,20 @@ __device__ __forceinline__ void bitonic_sort(Ptr a, int n, int logP)
 }
 
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_CAP = 4096;     // entries sorted in shared memory (32 KB); larger buckets sort in place in L2/HBM
+constexpr int SORT_CAP = 4096;                       // entries per tile sorted by sort_tiles (32 KB of smem + 16 KB of bins)
 constexpr int SORT_PER_THREAD = SORT_CAP / SORT_THREADS;
+constexpr int SORT_NET_CAP = 8192;                   // larger buckets: sorting network, in smem up to this size, else in place in L2/HBM
+constexpr int SORT_POP = 16;                         // tiles taken from the queue per atomic
+
 constexpr int SORT_MAX_BIN = 48;
-constexpr int SORT_NET_CAP = 8192; // the same 64 KB of shared memory holds this many entries for the sorting network alone   // a depth bin fuller than this sends the tile to the bitonic network instead
+// a depth bin fuller than SORT_MAX_BIN sends the tile to the bitonic network instead
 
 // One tile's bucket (n <= SORT_CAP entries in s_ent) sorted in O(n): entries are spread over B >= n depth bins
 // (bin = monotone linear map of the depth bits between the bucket's min and max), a scan of the bin counts gives
 // each bin its output range, and every bin (about one entry on average) is finished by an insertion sort on the
 // full 64-bit (depth bits, Gaussian) key.  Returns false (nothing guaranteed about s_ent's order) when the depths
 // are too clustered for that to be cheap; the caller then runs the bitonic network.
-__device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB)
+__device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB, int32_t *__restrict__ out)
 {
     __shared__ uint32_t s_red[2 * (SORT_THREADS / 32)];
     __shared__ uint32_t s_wsum[SORT_THREADS / 32];
@@ -259,24 +262,28 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB)
         if (i < n) s_ent[atomicAdd(&s_bin[bin[k]], 1u)] = ent[k];
     }
     __syncthreads();
-    // pass 3: s_bin[b] is now the END of bin b; insertion sort inside each bin
-    for (int b = threadIdx.x; b < B; b += SORT_THREADS) {
-        const int e0 = b == 0 ? 0 : (int)s_bin[b - 1], e1 = (int)s_bin[b];
-        for (int i = e0 + 1; i < e1; ++i) {
-            const uint64_t x = s_ent[i];
-            int j = i - 1;
-            while (j >= e0 && s_ent[j] > x) { s_ent[j + 1] = s_ent[j]; --j; }
-            s_ent[j + 1] = x;
+    // pass 3: s_bin[b] is now the END of bin b.  Every entry finds its final position = bin start + its rank among
+    // the (about one, at most SORT_MAX_BIN) entries of its bin, and its Gaussian index goes straight to the output.
+#pragma unroll
+    for (int k = 0; k < SORT_PER_THREAD; ++k) {
+        const int i = threadIdx.x + k * SORT_THREADS;
+        if (i < n) {
+            const int e0 = bin[k] == 0 ? 0 : (int)s_bin[bin[k] - 1], e1 = (int)s_bin[bin[k]];
+            int rank = e0;
+            for (int q = e0; q < e1; ++q) rank += s_ent[q] < ent[k];
+            out[rank] = (int32_t)(uint32_t)ent[k];
         }
     }
-    __syncthreads();
     return true;
 }
 
-// CTAs pull tiles from a device counter (bucket sizes range from 0 to thousands of entries).
-__global__ void __launch_bounds__(SORT_THREADS) sort_tiles(unsigned int num_tiles_total,
+// CTAs pull SORT_POP tiles at a time from a device counter (four tiles in five are empty: the queue pop, its two
+// barriers and the tile_start loads are amortised over the batch).  Buckets of up to SORT_CAP entries are sorted in
+// shared memory: rank sort for n <= 64, the O(n) depth-bin sort otherwise, the bitonic network when the depths are
+// too clustered for the bins.  Larger buckets are left to sort_tiles_large.
+__global__ void __launch_bounds__(SORT_THREADS, 4) sort_tiles(unsigned int num_tiles_total,
                                                             const uint32_t *__restrict__ tile_start,
-                                                            uint64_t *__restrict__ entries,
+                                                            const uint64_t *__restrict__ entries,
                                                             int32_t *__restrict__ point_list, int64_t capacity,
                                                             unsigned int *work_counter)
 {
@@ -284,40 +291,89 @@ __global__ void __launch_bounds__(SORT_THREADS) sort_tiles(unsigned int num_tile
     uint64_t *s_ent = s_sort;                                            // [SORT_CAP]
     uint32_t *s_bin = reinterpret_cast<uint32_t *>(s_sort + SORT_CAP);   // [SORT_CAP]
     __shared__ unsigned int s_next;
+    __shared__ uint32_t s_ts[SORT_POP + 1];
+    const int tid = threadIdx.x;
     for (;;) {
-        if (threadIdx.x == 0) s_next = atomicAdd(work_counter, 1u);
         __syncthreads();
-        const unsigned int t = s_next;
+        if (tid == 0) s_next = atomicAdd(work_counter, (unsigned int)SORT_POP);
         __syncthreads();
-        if (t >= num_tiles_total) break;
-        const int64_t s = tile_start[t];
-        int64_t e = tile_start[t + 1];
-        if (e > capacity) e = capacity;
-        const int n = (int)(e - s);
-        if (n <= 0) continue;
-        if (n == 1) {
-            if (threadIdx.x == 0) point_list[s] = (int32_t)(uint32_t)entries[s];
-            continue;
-        }
-        int logP = 1;
-        while ((1 << logP) < n) ++logP;
-        if (n <= SORT_CAP) {
-            for (int i = threadIdx.x; i < n; i += blockDim.x) s_ent[i] = entries[s + i];
+        const unsigned int t0 = s_next;
+        if (t0 >= num_tiles_total) break;
+        const unsigned int nt = min((unsigned int)SORT_POP, num_tiles_total - t0);
+        if (tid <= (int)nt) s_ts[tid] = tile_start[t0 + tid];
+        __syncthreads();
+        for (unsigned int q = 0; q < nt; ++q) {
+            const int64_t s = s_ts[q];
+            int64_t e = s_ts[q + 1];
+            if (e > capacity) e = capacity;
+            const int n = (int)(e - s);
+            if (n <= 0 || n > SORT_CAP) continue;                  // uniform across the CTA
+            if (n == 1) {
+                if (tid == 0) point_list[s] = (int32_t)(uint32_t)entries[s];
+                continue;
+            }
+            __syncthreads();                                       // the previous tile is done with shared memory
+            for (int i = tid; i < n; i += SORT_THREADS) s_ent[i] = entries[s + i];
             __syncthreads();
-            if (n <= 64 || !bin_sort_tile(s_ent, s_bin, n, logP < 8 ? 8 : logP)) {
+            if (n <= 64) {                                         // rank sort (keys are distinct)
+                if (tid < n) {
+                    const uint64_t x = s_ent[tid];
+                    int rank = 0;
+                    for (int u = 0; u < n; ++u) rank += s_ent[u] < x;
+                    point_list[s + rank] = (int32_t)(uint32_t)x;
+                }
+                continue;
+            }
+            int logP = 1;
+            while ((1 << logP) < n) ++logP;
+            if (!bin_sort_tile(s_ent, s_bin, n, logP < 8 ? 8 : logP, point_list + s)) {
                 __syncthreads();
                 bitonic_sort(s_ent, n, logP);
+                for (int i = tid; i < n; i += SORT_THREADS) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
             }
-            for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
-        } else if (n <= SORT_NET_CAP) {
-            for (int i = threadIdx.x; i < n; i += blockDim.x) s_ent[i] = entries[s + i];
+        }
+    }
+}
+
+// Buckets above SORT_CAP entries (dense close-ups, the 500k-Gaussian configuration): bitonic network in shared
+// memory up to SORT_NET_CAP entries, in place in global memory beyond.  CTAs scan the tile table in strides.
+__global__ void __launch_bounds__(SORT_THREADS) sort_tiles_large(unsigned int num_tiles_total,
+                                                                  const uint32_t *__restrict__ tile_start,
+                                                                  uint64_t *__restrict__ entries,
+                                                                  int32_t *__restrict__ point_list, int64_t capacity)
+{
+    extern __shared__ uint64_t s_big[];                            // [SORT_NET_CAP]
+    __shared__ unsigned int s_list[SORT_THREADS];
+    __shared__ unsigned int s_nbig;
+    for (unsigned int base = blockIdx.x * SORT_THREADS; base < num_tiles_total; base += gridDim.x * SORT_THREADS) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_nbig = 0u;
+        __syncthreads();
+        const unsigned int t = base + threadIdx.x;
+        if (t < num_tiles_total) {
+            const int64_t e = min((int64_t)tile_start[t + 1], capacity);
+            if (e - (int64_t)tile_start[t] > SORT_CAP) s_list[atomicAdd(&s_nbig, 1u)] = t;
+        }
+        __syncthreads();
+        const unsigned int nbig = s_nbig;
+        for (unsigned int q = 0; q < nbig; ++q) {
+            const unsigned int tt = s_list[q];
+            const int64_t s = tile_start[tt];
+            const int64_t e = min((int64_t)tile_start[tt + 1], capacity);
+            const int n = (int)(e - s);
+            int logP = 1;
+            while ((1 << logP) < n) ++logP;
             __syncthreads();
-            bitonic_sort(s_ent, n, logP);
-            for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
-        } else {
-            uint64_t *g = entries + s;
-            bitonic_sort(g, n, logP);
-            for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)g[i];
+            if (n <= SORT_NET_CAP) {
+                for (int i = threadIdx.x; i < n; i += blockDim.x) s_big[i] = entries[s + i];
+                __syncthreads();
+                bitonic_sort(s_big, n, logP);
+                for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)s_big[i];
+            } else {
+                uint64_t *g = entries + s;
+                bitonic_sort(g, n, logP);
+                for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)g[i];
+            }
         }
     }
 }
@@ -372,11 +428,17 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
         d->num_gaussians, gx, tiles, reinterpret_cast<const float4 *>(geom), reinterpret_cast<const ushort4 *>(rect),
         tile_start, tile_cursor, entries, capacity, overflow, use_smem);
     AMAV_CHECK_LAUNCH();
-    const int grid = (int)(nt < AMAV_SM_COUNT * 4 ? nt : AMAV_SM_COUNT * 4);
-    const int sort_smem = SORT_NET_CAP * 8;       // >= SORT_CAP * 12
-    cudaFuncSetAttribute(sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_smem);
-    sort_tiles<<<grid, SORT_THREADS, sort_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
-                                                  reinterpret_cast<unsigned int *>(overflow) + 1);
+    const int64_t want = (nt + SORT_POP - 1) / SORT_POP;
+    const int grid = (int)(want < AMAV_SM_COUNT * 5 ? want : AMAV_SM_COUNT * 5);
+    const int small_smem = SORT_CAP * 12;
+    cudaFuncSetAttribute(sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);
+    sort_tiles<<<grid, SORT_THREADS, small_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
+                                                           reinterpret_cast<unsigned int *>(overflow) + 1);
+    AMAV_CHECK_LAUNCH();
+    const int sort_smem = SORT_NET_CAP * 8;
+    cudaFuncSetAttribute(sort_tiles_large, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_smem);
+    sort_tiles_large<<<AMAV_SM_COUNT, SORT_THREADS, sort_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list,
+                                                                        capacity);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }
