@@ -188,47 +188,48 @@ __device__ __forceinline__ void bitonic_sort(Ptr a, int n, int logP)
     }
 }
 
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_CAP = 4096;                       // entries per tile sorted by sort_tiles (32 KB of smem + 16 KB of bins)
-constexpr int SORT_PER_THREAD = SORT_CAP / SORT_THREADS;
-constexpr int SORT_NET_CAP = 8192;                   // larger buckets: sorting network, in smem up to this size, else in place in L2/HBM
-constexpr int SORT_POP = 16;                         // tiles taken from the queue per atomic
+// Two instantiations of the per-tile sort share one body:
+//   sort_tiles<256, 4096, 16>    buckets of up to 4096 entries: 48 KB of smem, 4 CTAs per SM;
+//   sort_tiles<1024, 16384, 64>  buckets of 4097..16384 entries (512x512 training views, 500k-Gaussian close-ups):
+//                                192 KB of smem, one CTA per SM; larger buckets still: bitonic network in place in
+//                                global memory (L2).
+constexpr int SORT_SMALL_T = 256, SORT_SMALL_CAP = 4096, SORT_SMALL_POP = 16;
+constexpr int SORT_LARGE_T = 1024, SORT_LARGE_CAP = 16384, SORT_LARGE_POP = 64;
+constexpr int SORT_MAX_BIN = 48;                     // a depth bin fuller than this sends the tile to the bitonic network
 
-constexpr int SORT_MAX_BIN = 48;
-// a depth bin fuller than SORT_MAX_BIN sends the tile to the bitonic network instead
-
-// One tile's bucket (n <= SORT_CAP entries in s_ent) sorted in O(n): entries are spread over B >= n depth bins
+// One tile's bucket (n <= T * PER entries in s_ent) sorted in O(n): entries are spread over B >= n depth bins
 // (bin = monotone linear map of the depth bits between the bucket's min and max), a scan of the bin counts gives
-// each bin its output range, and every bin (about one entry on average) is finished by an insertion sort on the
-// full 64-bit (depth bits, Gaussian) key.  Returns false (nothing guaranteed about s_ent's order) when the depths
+// each bin its output range, and every entry's final position is its bin's start plus its rank among the (about
+// one) entries of the bin on the full 64-bit (depth bits, Gaussian) key.  Returns false (nothing guaranteed about s_ent's order) when the depths
 // are too clustered for that to be cheap; the caller then runs the bitonic network.
+template <int T, int PER>
 __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB, int32_t *__restrict__ out)
 {
-    __shared__ uint32_t s_red[2 * (SORT_THREADS / 32)];
-    __shared__ uint32_t s_wsum[SORT_THREADS / 32];
+    __shared__ uint32_t s_red[2 * (T / 32)];
+    __shared__ uint32_t s_wsum[T / 32];
     __shared__ int s_bad;
     const int B = 1 << logB;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t lo = 0xffffffffu, hi = 0u;
-    for (int i = threadIdx.x; i < n; i += SORT_THREADS) {
+    for (int i = threadIdx.x; i < n; i += T) {
         const uint32_t d = (uint32_t)(s_ent[i] >> 32);
         lo = min(lo, d); hi = max(hi, d);
     }
     lo = __reduce_min_sync(0xffffffffu, lo);
     hi = __reduce_max_sync(0xffffffffu, hi);
-    if (lane == 0) { s_red[warp] = lo; s_red[SORT_THREADS / 32 + warp] = hi; }
-    for (int i = threadIdx.x; i < B; i += SORT_THREADS) s_bin[i] = 0u;
+    if (lane == 0) { s_red[warp] = lo; s_red[T / 32 + warp] = hi; }
+    for (int i = threadIdx.x; i < B; i += T) s_bin[i] = 0u;
     if (threadIdx.x == 0) s_bad = 0;
     __syncthreads();
 #pragma unroll
-    for (int w = 0; w < SORT_THREADS / 32; ++w) { lo = min(lo, s_red[w]); hi = max(hi, s_red[SORT_THREADS / 32 + w]); }
+    for (int w = 0; w < T / 32; ++w) { lo = min(lo, s_red[w]); hi = max(hi, s_red[T / 32 + w]); }
     const float scale = (float)B / ((float)(hi - lo) + 1.0f);
     // pass 1: bin of every entry (kept in registers) + bin counts
-    uint64_t ent[SORT_PER_THREAD];
-    int bin[SORT_PER_THREAD];
+    uint64_t ent[PER];
+    int bin[PER];
 #pragma unroll
-    for (int k = 0; k < SORT_PER_THREAD; ++k) {
-        const int i = threadIdx.x + k * SORT_THREADS;
+    for (int k = 0; k < PER; ++k) {
+        const int i = threadIdx.x + k * T;
         if (i < n) {
             ent[k] = s_ent[i];
             bin[k] = min(B - 1, (int)((float)((uint32_t)(ent[k] >> 32) - lo) * scale));
@@ -236,8 +237,8 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB,
         }
     }
     __syncthreads();
-    // exclusive scan of the B bin counts (B / 256 consecutive bins per thread)
-    const int per = B >> 8;                               // B >= 256 is guaranteed by the caller
+    // exclusive scan of the B bin counts (B / T consecutive bins per thread)
+    const int per = B / T;                                // B >= T is guaranteed by the caller
     uint32_t sum = 0, mx = 0;
     for (int q = 0; q < per; ++q) { const uint32_t c = s_bin[threadIdx.x * per + q]; sum += c; mx = max(mx, c); }
     if (mx > SORT_MAX_BIN) s_bad = 1;
@@ -247,7 +248,7 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB,
     if (s_bad) return false;
     uint32_t base = inc - sum;
 #pragma unroll
-    for (int w = 0; w < SORT_THREADS / 32; ++w)
+    for (int w = 0; w < T / 32; ++w)
         if (w < warp) base += s_wsum[w];
     for (int q = 0; q < per; ++q) {
         const uint32_t c = s_bin[threadIdx.x * per + q];
@@ -257,16 +258,16 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB,
     __syncthreads();
     // pass 2: scatter (slot inside the bin from an atomic cursor: any order, the bin is sorted next)
 #pragma unroll
-    for (int k = 0; k < SORT_PER_THREAD; ++k) {
-        const int i = threadIdx.x + k * SORT_THREADS;
+    for (int k = 0; k < PER; ++k) {
+        const int i = threadIdx.x + k * T;
         if (i < n) s_ent[atomicAdd(&s_bin[bin[k]], 1u)] = ent[k];
     }
     __syncthreads();
     // pass 3: s_bin[b] is now the END of bin b.  Every entry finds its final position = bin start + its rank among
     // the (about one, at most SORT_MAX_BIN) entries of its bin, and its Gaussian index goes straight to the output.
 #pragma unroll
-    for (int k = 0; k < SORT_PER_THREAD; ++k) {
-        const int i = threadIdx.x + k * SORT_THREADS;
+    for (int k = 0; k < PER; ++k) {
+        const int i = threadIdx.x + k * T;
         if (i < n) {
             const int e0 = bin[k] == 0 ? 0 : (int)s_bin[bin[k] - 1], e1 = (int)s_bin[bin[k]];
             int rank = e0;
@@ -277,29 +278,30 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB,
     return true;
 }
 
-// CTAs pull SORT_POP tiles at a time from a device counter (four tiles in five are empty: the queue pop, its two
-// barriers and the tile_start loads are amortised over the batch).  Buckets of up to SORT_CAP entries are sorted in
-// shared memory: rank sort for n <= 64, the O(n) depth-bin sort otherwise, the bitonic network when the depths are
-// too clustered for the bins.  Larger buckets are left to sort_tiles_large.
-__global__ void __launch_bounds__(SORT_THREADS, 4) sort_tiles(unsigned int num_tiles_total,
-                                                            const uint32_t *__restrict__ tile_start,
-                                                            const uint64_t *__restrict__ entries,
-                                                            int32_t *__restrict__ point_list, int64_t capacity,
-                                                            unsigned int *work_counter)
+// CTAs pull POP tiles at a time from a device counter (four tiles in five are empty: the queue pop, its two barriers
+// and the tile_start loads are amortised over the batch).  A bucket of MINN < n <= CAP entries is sorted in shared
+// memory: rank sort for n <= 64, the O(n) depth-bin sort otherwise, the bitonic network when the depths are too
+// clustered for the bins; with GLOBAL_FALLBACK buckets above CAP are sorted in place in global memory.
+template <int T, int CAP, int POP, int MINN, bool GLOBAL_FALLBACK>
+__global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int num_tiles_total,
+                                                                  const uint32_t *__restrict__ tile_start,
+                                                                  uint64_t *__restrict__ entries,
+                                                                  int32_t *__restrict__ point_list, int64_t capacity,
+                                                                  unsigned int *work_counter)
 {
     extern __shared__ uint64_t s_sort[];
-    uint64_t *s_ent = s_sort;                                            // [SORT_CAP]
-    uint32_t *s_bin = reinterpret_cast<uint32_t *>(s_sort + SORT_CAP);   // [SORT_CAP]
+    uint64_t *s_ent = s_sort;                                            // [CAP]
+    uint32_t *s_bin = reinterpret_cast<uint32_t *>(s_sort + CAP);        // [CAP]
     __shared__ unsigned int s_next;
-    __shared__ uint32_t s_ts[SORT_POP + 1];
+    __shared__ uint32_t s_ts[POP + 1];
     const int tid = threadIdx.x;
     for (;;) {
         __syncthreads();
-        if (tid == 0) s_next = atomicAdd(work_counter, (unsigned int)SORT_POP);
+        if (tid == 0) s_next = atomicAdd(work_counter, (unsigned int)POP);
         __syncthreads();
         const unsigned int t0 = s_next;
         if (t0 >= num_tiles_total) break;
-        const unsigned int nt = min((unsigned int)SORT_POP, num_tiles_total - t0);
+        const unsigned int nt = min((unsigned int)POP, num_tiles_total - t0);
         if (tid <= (int)nt) s_ts[tid] = tile_start[t0 + tid];
         __syncthreads();
         for (unsigned int q = 0; q < nt; ++q) {
@@ -307,13 +309,21 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) sort_tiles(unsigned int num_t
             int64_t e = s_ts[q + 1];
             if (e > capacity) e = capacity;
             const int n = (int)(e - s);
-            if (n <= 0 || n > SORT_CAP) continue;                  // uniform across the CTA
+            if (n <= MINN || (!GLOBAL_FALLBACK && n > CAP)) continue;     // uniform across the CTA
             if (n == 1) {
                 if (tid == 0) point_list[s] = (int32_t)(uint32_t)entries[s];
                 continue;
             }
+            int logP = 1;
+            while ((1 << logP) < n) ++logP;
             __syncthreads();                                       // the previous tile is done with shared memory
-            for (int i = tid; i < n; i += SORT_THREADS) s_ent[i] = entries[s + i];
+            if (n > CAP) {
+                uint64_t *g = entries + s;
+                bitonic_sort(g, n, logP);
+                for (int i = tid; i < n; i += T) point_list[s + i] = (int32_t)(uint32_t)g[i];
+                continue;
+            }
+            for (int i = tid; i < n; i += T) s_ent[i] = entries[s + i];
             __syncthreads();
             if (n <= 64) {                                         // rank sort (keys are distinct)
                 if (tid < n) {
@@ -324,55 +334,12 @@ __global__ void __launch_bounds__(SORT_THREADS, 4) sort_tiles(unsigned int num_t
                 }
                 continue;
             }
-            int logP = 1;
-            while ((1 << logP) < n) ++logP;
-            if (!bin_sort_tile(s_ent, s_bin, n, logP < 8 ? 8 : logP, point_list + s)) {
+            int logB = logP;
+            while ((1 << logB) < T) ++logB;
+            if (!bin_sort_tile<T, CAP / T>(s_ent, s_bin, n, logB, point_list + s)) {
                 __syncthreads();
                 bitonic_sort(s_ent, n, logP);
-                for (int i = tid; i < n; i += SORT_THREADS) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
-            }
-        }
-    }
-}
-
-// Buckets above SORT_CAP entries (dense close-ups, the 500k-Gaussian configuration): bitonic network in shared
-// memory up to SORT_NET_CAP entries, in place in global memory beyond.  CTAs scan the tile table in strides.
-__global__ void __launch_bounds__(SORT_THREADS) sort_tiles_large(unsigned int num_tiles_total,
-                                                                  const uint32_t *__restrict__ tile_start,
-                                                                  uint64_t *__restrict__ entries,
-                                                                  int32_t *__restrict__ point_list, int64_t capacity)
-{
-    extern __shared__ uint64_t s_big[];                            // [SORT_NET_CAP]
-    __shared__ unsigned int s_list[SORT_THREADS];
-    __shared__ unsigned int s_nbig;
-    for (unsigned int base = blockIdx.x * SORT_THREADS; base < num_tiles_total; base += gridDim.x * SORT_THREADS) {
-        __syncthreads();
-        if (threadIdx.x == 0) s_nbig = 0u;
-        __syncthreads();
-        const unsigned int t = base + threadIdx.x;
-        if (t < num_tiles_total) {
-            const int64_t e = min((int64_t)tile_start[t + 1], capacity);
-            if (e - (int64_t)tile_start[t] > SORT_CAP) s_list[atomicAdd(&s_nbig, 1u)] = t;
-        }
-        __syncthreads();
-        const unsigned int nbig = s_nbig;
-        for (unsigned int q = 0; q < nbig; ++q) {
-            const unsigned int tt = s_list[q];
-            const int64_t s = tile_start[tt];
-            const int64_t e = min((int64_t)tile_start[tt + 1], capacity);
-            const int n = (int)(e - s);
-            int logP = 1;
-            while ((1 << logP) < n) ++logP;
-            __syncthreads();
-            if (n <= SORT_NET_CAP) {
-                for (int i = threadIdx.x; i < n; i += blockDim.x) s_big[i] = entries[s + i];
-                __syncthreads();
-                bitonic_sort(s_big, n, logP);
-                for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)s_big[i];
-            } else {
-                uint64_t *g = entries + s;
-                bitonic_sort(g, n, logP);
-                for (int i = threadIdx.x; i < n; i += blockDim.x) point_list[s + i] = (int32_t)(uint32_t)g[i];
+                for (int i = tid; i < n; i += T) point_list[s + i] = (int32_t)(uint32_t)s_ent[i];
             }
         }
     }
@@ -428,17 +395,24 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
         d->num_gaussians, gx, tiles, reinterpret_cast<const float4 *>(geom), reinterpret_cast<const ushort4 *>(rect),
         tile_start, tile_cursor, entries, capacity, overflow, use_smem);
     AMAV_CHECK_LAUNCH();
-    const int64_t want = (nt + SORT_POP - 1) / SORT_POP;
-    const int grid = (int)(want < AMAV_SM_COUNT * 5 ? want : AMAV_SM_COUNT * 5);
-    const int small_smem = SORT_CAP * 12;
-    cudaFuncSetAttribute(sort_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);
-    sort_tiles<<<grid, SORT_THREADS, small_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
-                                                           reinterpret_cast<unsigned int *>(overflow) + 1);
+    // small buckets: queue head = overflow[1]; large buckets: queue head = tile_cursor[0], free once the scatter is done
+    auto small = sort_tiles<SORT_SMALL_T, SORT_SMALL_CAP, SORT_SMALL_POP, 0, false>;
+    auto large = sort_tiles<SORT_LARGE_T, SORT_LARGE_CAP, SORT_LARGE_POP, SORT_SMALL_CAP, true>;
+    const int64_t want = (nt + SORT_SMALL_POP - 1) / SORT_SMALL_POP;
+    const int grid = (int)(want < AMAV_SM_COUNT * 4 ? want : AMAV_SM_COUNT * 4);
+    const int small_smem = SORT_SMALL_CAP * 12, large_smem = SORT_LARGE_CAP * 12;
+    cudaFuncSetAttribute(small, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);
+    cudaFuncSetAttribute(large, cudaFuncAttributeMaxDynamicSharedMemorySize, large_smem);
+    small<<<grid, SORT_SMALL_T, small_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
+                                                      reinterpret_cast<unsigned int *>(overflow) + 1);
     AMAV_CHECK_LAUNCH();
-    const int sort_smem = SORT_NET_CAP * 8;
-    cudaFuncSetAttribute(sort_tiles_large, cudaFuncAttributeMaxDynamicSharedMemorySize, sort_smem);
-    sort_tiles_large<<<AMAV_SM_COUNT, SORT_THREADS, sort_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list,
-                                                                        capacity);
+    if (cudaMemsetAsync(tile_cursor, 0, sizeof(uint32_t), stream) != cudaSuccess) {
+        amav_set_error("%s: cudaMemsetAsync failed", __func__);
+        return AMAV_ECUDA;
+    }
+    const int64_t wantl = (nt + SORT_LARGE_POP - 1) / SORT_LARGE_POP;
+    large<<<(int)(wantl < AMAV_SM_COUNT ? wantl : AMAV_SM_COUNT), SORT_LARGE_T, large_smem, stream>>>(
+        (unsigned int)nt, tile_start, entries, point_list, capacity, tile_cursor);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }

@@ -127,7 +127,7 @@ int amav_splat_preprocess(const AmavSplatDims *d, const float *means3d, const fl
  *     identifyTileRanges: tile t's sorted run is point_list[tile_start[t] : tile_start[t+1]], ordered
  *     by (depth bits, Gaussian index) = a stable sort of (tile<<32 | depth) keys.
  *   scan_tmp   [amav_splat_scan_tmp_elems(F*tiles)] uint32 scratch
- *   tile_cursor[F*tiles] uint32: MUST be zeroed by the caller
+ *   tile_cursor[F*tiles] uint32: MUST be zeroed by the caller (scratch: bucket cursors, then the large-bucket sort's queue head)
  *   entries    [capacity] uint64 scratch; point_list [capacity] int32 out (Gaussian index within the frame)
  *   overflow   [2] int32, MUST be zeroed by the caller: [0] is set to 1 (and binning truncated) when D > capacity;
  *              [1] is the sort kernel's tile queue head
