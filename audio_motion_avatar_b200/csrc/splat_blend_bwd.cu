@@ -35,13 +35,16 @@ struct BlendBwdParams {
 constexpr int NV = 9;                // accumulated values per Gaussian
 constexpr int ACC_LD = 9;            // row stride of the smem accumulator (odd: conflict-free flush)
 
-__global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendBwdParams p, const float *__restrict__ bg)
+__global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const BlendBwdParams p, const float *__restrict__ bg)
 {
-    __shared__ float4 s_g0[BLEND_THREADS];
-    __shared__ float4 s_g1[BLEND_THREADS];
-    __shared__ float4 s_g2[BLEND_THREADS];
-    __shared__ float s_acc[BLEND_THREADS * ACC_LD];
-    __shared__ int s_gid[BLEND_THREADS];
+    // double-buffered batch state: thread t stages record t of a batch, zeroes its accumulator row and later flushes
+    // it, so consecutive batches need ONE barrier between them (after staging); the flush of batch k overlaps the
+    // other warps' walk over batch k+1
+    __shared__ float4 s_g0b[2][BLEND_THREADS];
+    __shared__ float4 s_g1b[2][BLEND_THREADS];
+    __shared__ float4 s_g2b[2][BLEND_THREADS];
+    __shared__ float s_accb[2][BLEND_THREADS * ACC_LD];
+    __shared__ int s_gidb[2][BLEND_THREADS];
     __shared__ unsigned char s_list[BLEND_THREADS / 32][BLEND_THREADS];
     __shared__ unsigned int s_next;
     __shared__ int s_maxc;
@@ -98,21 +101,44 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendBwd
         float T = T_final, accum0 = 0.0f, accum1 = 0.0f, accum2 = 0.0f, last_alpha = 0.0f;
         float lc0 = 0.0f, lc1 = 0.0f, lc2 = 0.0f;
 
-        for (int b = (nproc - 1) >> 8; b >= 0 && nproc > 0; --b) {
+        // flush of one staged batch: one record per (tile, Gaussian)
+        auto flush = [&](int buf, int count) {
+            if ((int)threadIdx.x < count) {
+                const float *sa = s_accb[buf] + threadIdx.x * ACC_LD;
+                const float4 q0 = make_float4(sa[0], sa[1], sa[2], sa[3]);
+                const float4 q1 = make_float4(sa[4], sa[5], sa[6], sa[7]);
+                const float q2 = sa[8];
+                const bool nz = q0.x != 0.0f || q0.y != 0.0f || q0.z != 0.0f || q0.w != 0.0f || q1.x != 0.0f ||
+                                q1.y != 0.0f || q1.z != 0.0f || q1.w != 0.0f || q2 != 0.0f;
+                if (nz) {
+                    float *dst = dsum + (int64_t)s_gidb[buf][threadIdx.x] * 12;
+                    atomicAdd(reinterpret_cast<float4 *>(dst), q0);
+                    atomicAdd(reinterpret_cast<float4 *>(dst) + 1, q1);
+                    atomicAdd(dst + 8, q2);
+                }
+            }
+        };
+        int prev_nb = 0, it = 0;
+        for (int b = (nproc - 1) >> 8; b >= 0 && nproc > 0; --b, ++it) {
             const int before = b * BLEND_THREADS;
             const int nb = min(BLEND_THREADS, nproc - before);
-            __syncthreads();                                   // previous batch's flush has drained s_acc / s_g*
+            const int buf = it & 1;
+            float4 *s_g0 = s_g0b[buf], *s_g1 = s_g1b[buf], *s_g2 = s_g2b[buf];
+            float *s_acc = s_accb[buf];
+            // buffer `buf` was flushed by this same thread two batches ago: no barrier needed before re-staging it
             if ((int)threadIdx.x < nb) {
                 const int g = p.point_list[r0 + before + threadIdx.x];
                 const float4 *src = geom + 3 * (int64_t)g;
                 s_g0[threadIdx.x] = src[0];
                 s_g1[threadIdx.x] = src[1];
                 s_g2[threadIdx.x] = src[2];
-                s_gid[threadIdx.x] = g;
+                s_gidb[buf][threadIdx.x] = g;
             }
 #pragma unroll
             for (int k = 0; k < ACC_LD; ++k) s_acc[threadIdx.x * ACC_LD + k] = 0.0f;
-            __syncthreads();
+            __syncthreads();                                   // batch staged; every warp has finished the previous batch
+            flush(buf ^ 1, prev_nb);
+            prev_nb = nb;
             // this warp's list for the batch (list order), entries beyond the warp's deepest contributor dropped
             int cnt = 0;
             if (wmax > before) {
@@ -198,23 +224,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_bwd_kernel(const BlendBwd
                 if ((lane & 3) == 0) atomicAdd(&s_acc[j * ACC_LD + my_slot], v[0]);
                 else if (lane == 1) atomicAdd(&s_acc[j * ACC_LD + 8], v8);
             }
-            __syncthreads();
-            // flush: one record per (tile, Gaussian)
-            if ((int)threadIdx.x < nb) {
-                const float *s = s_acc + threadIdx.x * ACC_LD;
-                const float4 q0 = make_float4(s[0], s[1], s[2], s[3]);
-                const float4 q1 = make_float4(s[4], s[5], s[6], s[7]);
-                const float q2 = s[8];
-                const bool nz = q0.x != 0.0f || q0.y != 0.0f || q0.z != 0.0f || q0.w != 0.0f || q1.x != 0.0f ||
-                                q1.y != 0.0f || q1.z != 0.0f || q1.w != 0.0f || q2 != 0.0f;
-                if (nz) {
-                    float *dst = dsum + (int64_t)s_gid[threadIdx.x] * 12;
-                    atomicAdd(reinterpret_cast<float4 *>(dst), q0);
-                    atomicAdd(reinterpret_cast<float4 *>(dst) + 1, q1);
-                    atomicAdd(dst + 8, q2);
-                }
-            }
         }
+        __syncthreads();                                       // every warp is done with the last batch
+        flush((it - 1) & 1, prev_nb);
         __syncthreads();
     }
 }
@@ -240,7 +252,7 @@ extern "C" int amav_splat_blend_backward(const AmavSplatDims *d, const float *ge
     p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity;
     const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;
     AMAV_CHECK_ARG(total_tiles < ((int64_t)1 << 31), "too many tiles");
-    const int grid = (int)(total_tiles < AMAV_SM_COUNT * 6 ? total_tiles : AMAV_SM_COUNT * 6);
+    const int grid = (int)(total_tiles < AMAV_SM_COUNT * 4 ? total_tiles : AMAV_SM_COUNT * 4);
     blend_bwd_kernel<<<grid, BLEND_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;

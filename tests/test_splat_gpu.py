@@ -78,15 +78,18 @@ def test_splat_empty_and_degenerate():
     assert torch.all(o0["color"] == 0.0)
 
 
-def test_splat_large_bucket_sorts_in_global_memory():
-    # > 8192 Gaussians stacked on one tile: exercises the in-place (non shared-memory) bucket sort; the other tiles
-    # hold 4096..8192 entries (sorting network in shared memory) and fewer (depth-bin sort)
-    N, W, H = 12000, 32, 32
+@pytest.mark.parametrize("N,min_largest", [(12000, 8192), (24000, 16384)])
+def test_splat_large_buckets(N, min_largest):
+    # Thousands of Gaussians stacked on a few tiles.  12000: buckets of 4097..16384 entries (the 1024-thread
+    # shared-memory instantiation of the per-tile sort) next to small ones; 24000: a bucket above 16384 entries
+    # (bitonic network in place in global memory).
+    W, H = 32, 32
     sc = random_scene(N, W, H, seed=5, spread=0.05, smin=0.002, smax=0.004)
     sc["opac"] *= 0.02
     view, full, tan, outs = oracle_frames(sc, H, W)
     pre, binned, img = outs[0]
-    assert (binned["ranges"][:, 1] - binned["ranges"][:, 0]).max() > 8192
+    sizes = binned["ranges"][:, 1] - binned["ranges"][:, 0]
+    assert sizes.max() > min_largest and (N > 16384 or sizes.max() <= 16384)
     out = _run_cuda(sc, view, full, tan, H, W, (1.0, 1.0, 1.0))
     _check_frame(out, 0, pre, binned, img, N, H, W)
 
