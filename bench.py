@@ -302,8 +302,15 @@ def run_ours(args):
         per_stage[name] = {"ms": round(sms, 4), "algorithmic_bytes": by, "gbs": round(by / (sms * 1e-3) / 1e9, 1),
                            "frac": round(by / (sms * 1e-3) / 1e9 / peak, 4)}
     top = max(stages_ms, key=stages_ms.get)
+    traffic = None                                   # DRAM bytes per launch of the dominant kernel from the committed ncu capture
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as fh:
+            tj = json.load(fh)
+        if tj["workload"] == {"frames": Fr, "gaussians": N, "size": size}:
+            traffic = tj["bytes_per_launch"].get(top)
     roofline = {"kernel": top, "bound": "hbm", "achieved": per_stage[top]["gbs"], "peak": peak, "unit": "GB/s",
-                "frac": per_stage[top]["frac"], "traffic": None, "peak_source": peak_src,
+                "frac": per_stage[top]["frac"], "traffic": traffic, "peak_source": peak_src,
                 "share_of_step": round(stages_ms[top] / ms_per_step, 4), "stages": per_stage,
                 "entries_D": D, "entries_per_frame": D // max(Fr, 1)}
 
