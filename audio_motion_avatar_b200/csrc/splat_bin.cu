@@ -304,6 +304,10 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
         const unsigned int nt = min((unsigned int)POP, num_tiles_total - t0);
         if (tid <= (int)nt) s_ts[tid] = tile_start[t0 + tid];
         __syncthreads();
+        if (MINN > 0) {                                            // large-bucket instantiation: most batches hold none
+            const bool mine = tid < (int)nt && (int64_t)s_ts[tid + 1] - (int64_t)s_ts[tid] > MINN;
+            if (!__syncthreads_or(mine)) continue;
+        }
         for (unsigned int q = 0; q < nt; ++q) {
             const int64_t s = s_ts[q];
             int64_t e = s_ts[q + 1];
