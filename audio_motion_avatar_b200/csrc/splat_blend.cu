@@ -28,9 +28,9 @@ struct BlendParams {
 
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams p, const float *__restrict__ bg)
 {
-    __shared__ float4 s_g0[BLEND_THREADS];     // x, y, -conic.x/2, -conic.y
-    __shared__ float4 s_g1[BLEND_THREADS];     // -conic.z/2, opacity, pmin, r
-    __shared__ float4 s_g2[BLEND_THREADS];     // g, b, depth, radius
+    // one 48-byte record per staged entry: (x, y, -conic.x/2, -conic.y)(-conic.z/2, opacity, pmin, r)(g, b, depth, radius);
+    // a single array so the list walk needs one address computation per entry (immediate offsets for the rest)
+    __shared__ float4 s_rec[BLEND_THREADS * 3];
     __shared__ unsigned char s_list[BLEND_THREADS / 32][BLEND_THREADS];   // per warp: batch entries that touch its rectangle
     __shared__ unsigned int s_next;
     const int tiles = p.gx * p.gy;
@@ -70,9 +70,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             if (base + threadIdx.x < r1) {
                 const int g = p.point_list[base + threadIdx.x];
                 const float4 *src = geom + 3 * (int64_t)g;
-                s_g0[threadIdx.x] = src[0];
-                s_g1[threadIdx.x] = src[1];
-                s_g2[threadIdx.x] = src[2];
+                s_rec[3 * threadIdx.x] = src[0];
+                s_rec[3 * threadIdx.x + 1] = src[1];
+                s_rec[3 * threadIdx.x + 2] = src[2];
             }
             __syncthreads();
             const int nb = todo < BLEND_THREADS ? todo : BLEND_THREADS;
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             int cnt = 0;
             for (int j0 = 0; j0 < nb; j0 += 32) {
                 const int j = j0 + lane;
-                const bool keep = j < nb && warp_rect_keep(s_g0[j], s_g1[j], rx0, ry0);
+                const bool keep = j < nb && warp_rect_keep(s_rec[3 * j], s_rec[3 * j + 1], rx0, ry0);
                 const unsigned int m = __ballot_sync(0xffffffffu, keep);
                 if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned char)j;
                 cnt += __popc(m);
@@ -90,8 +90,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             // 2. exact per-pixel blend over the warp's list (same arithmetic and tests as the oracle)
             for (int k = 0; k < cnt; ++k) {
                 const int j = list[k];
-                const float4 a = s_g0[j];
-                const float4 b = s_g1[j];
+                const float4 *rec = s_rec + 3 * j;
+                const float4 a = rec[0];
+                const float4 b = rec[1];
                 const float dx = a.x - pxf, dy = a.y - pyf;
                 const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (b.x * dy) * dy);
                 if (done || power > 0.0f || power < b.z) continue;      // b.z = pmin: alpha surely < 1/255
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
                 const float Tn = T * (1.0f - alpha);
                 if (Tn < 0.0001f) { done = true; continue; }
                 const float w = alpha * T;
-                const float4 c = s_g2[j];
+                const float4 c = rec[2];
                 C0 = fmaf(b.w, w, C0);
                 C1 = fmaf(c.x, w, C1);
                 C2 = fmaf(c.y, w, C2);
