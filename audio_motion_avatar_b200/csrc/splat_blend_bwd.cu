@@ -40,9 +40,7 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
     // double-buffered batch state: thread t stages record t of a batch, zeroes its accumulator row and later flushes
     // it, so consecutive batches need ONE barrier between them (after staging); the flush of batch k overlaps the
     // other warps' walk over batch k+1
-    __shared__ float4 s_g0b[2][BLEND_THREADS];
-    __shared__ float4 s_g1b[2][BLEND_THREADS];
-    __shared__ float4 s_g2b[2][BLEND_THREADS];
+    __shared__ float4 s_recb[2][BLEND_THREADS * 3];          // 48-byte records, as in the forward kernel
     __shared__ float s_accb[2][BLEND_THREADS * ACC_LD];
     __shared__ int s_gidb[2][BLEND_THREADS];
     __shared__ unsigned char s_list[BLEND_THREADS / 32][BLEND_THREADS];
@@ -123,15 +121,15 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
             const int before = b * BLEND_THREADS;
             const int nb = min(BLEND_THREADS, nproc - before);
             const int buf = it & 1;
-            float4 *s_g0 = s_g0b[buf], *s_g1 = s_g1b[buf], *s_g2 = s_g2b[buf];
+            float4 *s_rec = s_recb[buf];
             float *s_acc = s_accb[buf];
             // buffer `buf` was flushed by this same thread two batches ago: no barrier needed before re-staging it
             if ((int)threadIdx.x < nb) {
                 const int g = p.point_list[r0 + before + threadIdx.x];
                 const float4 *src = geom + 3 * (int64_t)g;
-                s_g0[threadIdx.x] = src[0];
-                s_g1[threadIdx.x] = src[1];
-                s_g2[threadIdx.x] = src[2];
+                s_rec[3 * threadIdx.x] = src[0];
+                s_rec[3 * threadIdx.x + 1] = src[1];
+                s_rec[3 * threadIdx.x + 2] = src[2];
                 s_gidb[buf][threadIdx.x] = g;
             }
 #pragma unroll
@@ -145,7 +143,7 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
                 const int lim = min(nb, wmax - before);
                 for (int j0 = 0; j0 < lim; j0 += 32) {
                     const int j = j0 + lane;
-                    const bool keep = j < lim && warp_rect_keep(s_g0[j], s_g1[j], rx0, ry0);
+                    const bool keep = j < lim && warp_rect_keep(s_rec[3 * j], s_rec[3 * j + 1], rx0, ry0);
                     const unsigned int m = __ballot_sync(0xffffffffu, keep);
                     if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned char)j;
                     cnt += __popc(m);
@@ -154,8 +152,9 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
             __syncwarp();
             for (int k = cnt - 1; k >= 0; --k) {
                 const int j = list[k];
-                const float4 a = s_g0[j];
-                const float4 bq = s_g1[j];
+                const float4 *rec = s_rec + 3 * j;
+                const float4 a = rec[0];
+                const float4 bq = rec[1];
                 const float dx = a.x - pxf, dy = a.y - pyf;
                 const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (bq.x * dy) * dy);
                 bool use = (before + j + 1 <= last_contributor) && !(power > 0.0f) && !(power < bq.z);
@@ -170,7 +169,7 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
 #pragma unroll
                 for (int q = 0; q < 8; ++q) v[q] = 0.0f;
                 if (use) {
-                    const float4 c = s_g2[j];
+                    const float4 c = rec[2];
                     const float om = 1.0f - alpha;
                     T = T / om;
                     const float w = alpha * T;
