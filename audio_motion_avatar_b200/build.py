@@ -23,6 +23,7 @@ SOURCES = [
     ("triplane_bwd.cu", []),
     ("lbs.cu", []),
     ("lbs_bwd.cu", []),
+    ("image_loss.cu", []),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
           "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]

@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--no-gather", action="store_true")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "train"],
                     help="sequence = BASELINE.json configs[1] (the headline metric); train = configs[3], a secondary line")
+    ap.add_argument("--loss", default="l1_ssim", choices=["l1_ssim", "l1_torch"],
+                    help="train workload: fused l1 + 0.1 (1 - ssim) kernels (lightning_model_wrapper.py:138-140) or a plain torch L1")
     ap.add_argument("--subjects", type=int, default=4)
     ap.add_argument("--views", type=int, default=4)
     return ap.parse_args()
@@ -362,11 +364,11 @@ def run_ours(args):
 
 def run_train(args):
     """BASELINE.json configs[3]: one training step = `subjects` Gaussian sets (each its own triplane and pose) decoded
-    once and rendered from `views` cameras, 100k Gaussians, 512x512, L1 image loss, full backward through the splat,
+    once and rendered from `views` cameras, 100k Gaussians, 512x512, l1 + 0.1 (1 - ssim) image loss, full backward through the splat,
     the decode / triplane query and LBS, SGD step on the decoder.  N > 1: views are sharded over ranks (each rank
     renders `views` views of the same subjects: weak scaling) and dL/dtokens + decoder gradients are all-reduced."""
     import torch.distributed as dist
-    from audio_motion_avatar_b200 import _lib, synthetic as S
+    from audio_motion_avatar_b200 import _lib, losses, synthetic as S
     from audio_motion_avatar_b200.renderer import Renderer, render_multi_view
     from audio_motion_avatar_b200.shard import allreduce_gradients
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -399,16 +401,21 @@ def run_train(args):
     opt = torch.optim.SGD(r.gaussian_decoder.parameters(), lr=1e-4)
     leaves = [tokens] + list(pose_leaves.values())
 
+    if args.loss == "l1_ssim":
+        image_loss = lambda a, b: losses.l1_ssim_loss(a, b)[0]
+    else:
+        image_loss = lambda a, b: (a - b).abs().mean()
+
     def step():
         opt.zero_grad(set_to_none=True)
         for t in leaves:
             t.grad = None
         first = {k: v[:, :1] for k, v in cams.items()}
         img, gs = r(tokens, first, None, params)                                     # decode + view 0
-        loss = (img - target[:, :1]).abs().mean()
+        loss = image_loss(img, target[:, :1])
         if Tv > 1:
             mv = render_multi_view(gs, cams["intrinsic"][:, 1:], cams["extrinsic"][:, 1:], r.cfg)
-            loss = (loss + (mv - target[:, 1:]).abs().mean() * (Tv - 1)) / Tv
+            loss = (loss + image_loss(mv, target[:, 1:]) * (Tv - 1)) / Tv
         loss.backward()
         if world > 1:
             allreduce_gradients([tokens.grad] + [p.grad for p in r.gaussian_decoder.parameters()])
@@ -447,7 +454,7 @@ def run_train(args):
     line = {"metric": "training renders/sec (fwd+bwd) @100k Gaussians 512^2", "value": world * B * Tv / (ms_per_step * 1e-3),
             "unit": "(subject,view) renders/s", "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"training step: {B} subjects x {Tv} views per rank, {N} Gaussians, {size}x{size}, forward + "
+            "config": {"workload": f"training step: {B} subjects x {Tv} views per rank, {N} Gaussians, {size}x{size}, loss {args.loss}, forward + "
                                    "backward through splat, decode/triplane query and LBS, SGD on the decoder "
                                    "(BASELINE.json configs[3])",
                        "parallelism": f"view-sharded x{world}" + ("" if world == 1 else " + NCCL all-reduce of dL/dtokens and decoder grads")},

@@ -217,6 +217,21 @@ int amav_lbs_backward(int F, int V, int J, int S, const float *full_pose, const 
                       const float *v_posed, const float *d_verts, float *d_v_posed, float *d_A,
                       float *d_pose_feature, float *d_full_pose, float *d_shape, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Image losses of the training step (src/utils/loss_utils.py:18 l1_loss, :44-83 ssim; combined at
+ * lightning_model_wrapper.py:138-145) on the HWC frames the blend writes, and their gradient w.r.t. the rendered image.
+ *   img, gt [F,H,W,3];  11x11 Gaussian window (sigma 1.5), zero padding, C1 = 0.01^2, C2 = 0.03^2.
+ * amav_image_loss_forward:  sums [F,2], MUST be zeroed by the caller: [f][0] += sum |img - gt|, [f][1] += sum of the SSIM
+ *                           map over the frame's H*W*3 values; maps [F,3,3,H,W] (may be NULL when no gradient is wanted):
+ *                           dS/dmu1, dS/dE[x^2], dS/dE[xy] per channel.
+ * amav_image_loss_backward: grad [F,H,W,3] = g_l1[f] * sign(img - gt) + g_ssim[f] * d(sum SSIM map)/d(img)
+ *                           (g_l1, g_ssim: DEVICE arrays [F]; e.g. 1/n and -0.1/n for l1 + 0.1 * (1 - ssim)).
+ */
+int amav_image_loss_forward(int F, int H, int W, const float *img, const float *gt, float *sums, float *maps,
+                            void *stream);
+int amav_image_loss_backward(int F, int H, int W, const float *img, const float *gt, const float *maps,
+                             const float *g_l1, const float *g_ssim, float *grad, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -60,3 +60,20 @@ def test_grid_sample_baseline_equals_explicit_restatement(golden_dir):
     a = O.sample_from_triplane_torch(tri, pts, float(g["radius"]))
     assert (a - torch.from_numpy(g["feats"])).abs().max().item() <= 1e-6
     assert (a - O.sample_from_triplane(tri, pts, float(g["radius"]))).abs().max().item() <= 2e-6
+
+
+def test_image_losses_match_reference():
+    """oracle/loss_oracle.py vs the reference's own l1_loss / ssim and autograd through them (ref_loss.npz)."""
+    import os
+    from oracle import loss_oracle as L
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_loss.npz"))
+    img = torch.from_numpy(d["img"]).clone().requires_grad_(True)
+    gt = torch.from_numpy(d["gt"])
+    l1, s = L.l1_loss(img, gt), L.ssim(img, gt)
+    assert abs(l1.item() - float(d["l1"])) <= 1e-7 and abs(s.item() - float(d["ssim"])) <= 1e-6
+    per = L.ssim(img, gt, size_average=False)
+    assert np.abs(per.detach().numpy() - d["ssim_per_frame"]).max() <= 1e-6
+    loss = L.l1_ssim_loss(img, gt)
+    assert abs(loss.item() - float(d["loss"])) <= 1e-6
+    loss.backward()
+    assert np.abs(img.grad.numpy() - d["grad"]).max() <= 1e-9 + 1e-5 * np.abs(d["grad"]).max()
