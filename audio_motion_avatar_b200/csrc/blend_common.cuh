@@ -5,29 +5,82 @@
 
 namespace amav_blend {
 
-// exp(x), x <= 0: same operation sequence as amav_oracle_exp().
+// exp(x) for -87 < x <= 0: same operation sequence as amav_oracle_exp() (which also clamps x to >= -80; the blend
+// kernels only call this with power >= pmin, and preprocess stores pmin >= -80).  12 instructions: range reduction
+// by one FMA against the 1.5*2^23 magic constant, degree-5 minimax polynomial of 2^f on [-0.5, 0.5] (1.5 ulp
+// over the whole range; CUDA's expf, which upstream calls, is 2 ulp), exponent inserted by an integer add.
 __device__ __forceinline__ float amav_exp(float x)
 {
-    x = fmaxf(x, -80.0f);
     const float L2E_HI = 1.44269502162933349609375f;
     const float L2E_LO = 1.925963033500011e-8f;
     const float MAGIC = 12582912.0f;
-    const float t = x * L2E_HI;
-    const float r = t + MAGIC;
+    const float r = fmaf(x, L2E_HI, MAGIC);
     const float n = r - MAGIC;
     float f = fmaf(x, L2E_HI, -n);
     f = fmaf(x, L2E_LO, f);
-    float p = 1.5252733804059840e-5f;
-    p = fmaf(p, f, 1.5403530393381610e-4f);
-    p = fmaf(p, f, 1.3333558146428443e-3f);
-    p = fmaf(p, f, 9.6181291076284772e-3f);
-    p = fmaf(p, f, 5.5504108664821580e-2f);
-    p = fmaf(p, f, 2.4022650695910071e-1f);
-    p = fmaf(p, f, 6.9314718055994531e-1f);
+    float p = 0.001326472731307149f;
+    p = fmaf(p, f, 0.009671512991189957f);
+    p = fmaf(p, f, 0.05550733581185341f);
+    p = fmaf(p, f, 0.24022242426872253f);
+    p = fmaf(p, f, 0.6931470036506653f);
     p = fmaf(p, f, 1.0f);
     // r = MAGIC + n exactly, so the low mantissa bits of r hold n (two's complement): p * 2^n
     const int ni = __float_as_int(r) - __float_as_int(MAGIC);
     return __int_as_float(__float_as_int(p) + (ni << 23));
+}
+
+// amav_exp has two FFMAs with two constant operands each (x * log2e + MAGIC, c5 * f + c4); an FFMA takes one
+// immediate, and ptxas rematerialises the other constant (immediate move, parameter load or uniform-register copy)
+// inside the list walk: 2 of ~44 instructions per pair.  A value that comes out of a volatile shared-memory load at
+// a per-thread address cannot be rematerialised and is not promoted to a uniform register, so it stays in a plain
+// register.  Call once per kernel with a 4-float shared scratch; contains a barrier.  amav_exp(x, ec) is
+// bit-identical to amav_exp(x).
+struct ExpConsts { float magic, c5; };
+__device__ __forceinline__ ExpConsts exp_consts(float *s_scratch)
+{
+    if (threadIdx.x == 0) {
+        s_scratch[0] = s_scratch[1] = 12582912.0f;
+        s_scratch[2] = s_scratch[3] = 0.001326472731307149f;
+    }
+    __syncthreads();
+    ExpConsts ec;
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(s_scratch) + 4u * (threadIdx.x & 1u);
+    asm volatile("ld.volatile.shared.f32 %0, [%1];" : "=f"(ec.magic) : "r"(a));
+    asm volatile("ld.volatile.shared.f32 %0, [%1+8];" : "=f"(ec.c5) : "r"(a));
+    return ec;
+}
+__device__ __forceinline__ float amav_exp(float x, const ExpConsts ec)
+{
+    const float L2E_HI = 1.44269502162933349609375f;
+    const float L2E_LO = 1.925963033500011e-8f;
+    const float MAGIC = 12582912.0f;
+    const float r = fmaf(x, L2E_HI, ec.magic);
+    const float n = r - MAGIC;
+    float f = fmaf(x, L2E_HI, -n);
+    f = fmaf(x, L2E_LO, f);
+    float p = fmaf(ec.c5, f, 0.009671512991189957f);
+    p = fmaf(p, f, 0.05550733581185341f);
+    p = fmaf(p, f, 0.24022242426872253f);
+    p = fmaf(p, f, 0.6931470036506653f);
+    p = fmaf(p, f, 1.0f);
+    const int ni = __float_as_int(r) - __float_as_int(MAGIC);
+    return __int_as_float(__float_as_int(p) + (ni << 23));
+}
+
+// 16-byte shared-memory load at a 32-bit shared address + immediate offset.  The list walk addresses its records
+// as base + 48 j with the base held in a register; through a generic pointer ptxas rebuilds the shared window
+// base (S2R SR_CgaCtaId + LEA) for every entry.
+template <int OFF> __device__ __forceinline__ float4 lds128(uint32_t addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr), "n"(OFF));
+    return v;
+}
+template <int OFF> __device__ __forceinline__ float2 lds64(uint32_t addr)
+{
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(addr), "n"(OFF));
+    return v;
 }
 
 constexpr int BLEND_THREADS = 256;

@@ -26,12 +26,14 @@ struct BlendParams {
     uint32_t capacity;
 };
 
+template <bool DEPTH>
 __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams p, const float *__restrict__ bg)
 {
     // one 48-byte record per staged entry: (x, y, -conic.x/2, -conic.y)(-conic.z/2, opacity, pmin, r)(g, b, depth, radius);
-    // a single array so the list walk needs one address computation per entry (immediate offsets for the rest)
+    // a single array so the list walk needs one address per entry (immediate offsets for the rest)
     __shared__ float4 s_rec[BLEND_THREADS * 3];
-    __shared__ unsigned char s_list[BLEND_THREADS / 32][BLEND_THREADS];   // per warp: batch entries that touch its rectangle
+    // per warp: byte offsets (48 j) of the batch entries that touch its rectangle
+    __shared__ unsigned short s_list[BLEND_THREADS / 32][BLEND_THREADS];
     __shared__ unsigned int s_next;
     const int tiles = p.gx * p.gy;
     const unsigned int total_tiles = (unsigned int)((int64_t)p.F * tiles);
@@ -40,7 +42,13 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
     const int sx = (warp & 1) * SUB_W, sy = (warp >> 1) * SUB_H;
     const int lx = sx + (lane & (SUB_W - 1)), ly = sy + (lane >> 3);
     const float alpha_min = 1.0f / 255.0f;
-    unsigned char *list = s_list[warp];
+    unsigned short *list = s_list[warp];
+    // the record base as a 32-bit shared address held in a register: the output of a volatile asm is not
+    // rematerialised (through a generic pointer ptxas rebuilds the shared window base, S2R + LEA, for every entry)
+    uint32_t rec_base;
+    asm volatile("mov.u32 %0, %1;" : "=r"(rec_base) : "r"((uint32_t)__cvta_generic_to_shared(s_rec)));
+    __shared__ float s_expc[4];
+    const ExpConsts ec = exp_consts(s_expc);
 
     for (;;) {
         // tiles differ in depth by orders of magnitude (the body covers ~20% of the image): CTAs pull the next
@@ -61,12 +69,14 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
         const uint32_t r0 = min(p.tile_start[t], p.capacity), r1 = min(p.tile_start[t + 1], p.capacity);
         const float4 *geom = p.geom + (int64_t)f * p.N * 3;
 
-        float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dv = 0.0f;
+        // A saturated pixel (upstream: done) is marked by T = 0 with its transmittance parked in Tsat: every later
+        // pair then fails the Tn >= 1e-4 test by itself, so the list walk carries no flag (T > 0 while live: it only
+        // ever takes values Tn >= 1e-4).  Pixels outside the image start saturated.
+        float T = inside ? 1.0f : 0.0f, Tsat = 0.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dv = 0.0f;
         int last = 0, before = 0;                 // `before`: list entries in earlier batches (upstream's contributor count)
-        bool done = !inside;
         int todo = (int)(r1 - r0);
         for (uint32_t base = r0; base < r1; base += BLEND_THREADS, todo -= BLEND_THREADS, before += BLEND_THREADS) {
-            if (__syncthreads_count(done) == BLEND_THREADS) break;
+            if (__syncthreads_count(T == 0.0f) == BLEND_THREADS) break;
             if (base + threadIdx.x < r1) {
                 const int g = p.point_list[base + threadIdx.x];
                 const float4 *src = geom + 3 * (int64_t)g;
@@ -76,41 +86,44 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             }
             __syncthreads();
             const int nb = todo < BLEND_THREADS ? todo : BLEND_THREADS;
-            if (__all_sync(0xffffffffu, done)) continue;
+            if (__all_sync(0xffffffffu, T == 0.0f)) continue;
             // 1. this warp's list: batch entries whose footprint can reach its 8x4 rectangle, in list order
             int cnt = 0;
             for (int j0 = 0; j0 < nb; j0 += 32) {
                 const int j = j0 + lane;
                 const bool keep = j < nb && warp_rect_keep(s_rec[3 * j], s_rec[3 * j + 1], rx0, ry0);
                 const unsigned int m = __ballot_sync(0xffffffffu, keep);
-                if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned char)j;
+                if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(48 * j);
                 cnt += __popc(m);
             }
             __syncwarp();
             // 2. exact per-pixel blend over the warp's list (same arithmetic and tests as the oracle)
+            int last_off = -1;
             for (int k = 0; k < cnt; ++k) {
-                const int j = list[k];
-                const float4 *rec = s_rec + 3 * j;
-                const float4 a = rec[0];
-                const float4 b = rec[1];
+                const uint32_t off = list[k];
+                const uint32_t rec = rec_base + off;
+                const float4 a = lds128<0>(rec);
+                const float4 b = lds128<16>(rec);
                 const float dx = a.x - pxf, dy = a.y - pyf;
                 const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (b.x * dy) * dy);
-                if (done || power > 0.0f || power < b.z) continue;      // b.z = pmin: alpha surely < 1/255
-                const float alpha = fminf(0.99f, b.y * amav_exp(power));
+                if (power > 0.0f || power < b.z) continue;              // b.z = pmin: alpha surely < 1/255
+                const float alpha = fminf(0.99f, b.y * amav_exp(power, ec));
                 if (alpha < alpha_min) continue;
                 const float Tn = T * (1.0f - alpha);
-                if (Tn < 0.0001f) { done = true; continue; }
+                if (Tn < 0.0001f) { Tsat = fmaxf(Tsat, T); T = 0.0f; continue; }
                 const float w = alpha * T;
-                const float4 c = rec[2];
+                const float2 c = lds64<32>(rec);
                 C0 = fmaf(b.w, w, C0);
                 C1 = fmaf(c.x, w, C1);
                 C2 = fmaf(c.y, w, C2);
-                if (p.out_invdepth) Dv = fmaf(1.0f / c.z, w, Dv);
+                if (DEPTH) Dv = fmaf(1.0f / lds64<40>(rec).x, w, Dv);
                 T = Tn;
-                last = before + j + 1;
+                last_off = (int)off;
             }
+            if (last_off >= 0) last = before + last_off / 48 + 1;
         }
         if (inside) {
+            if (T == 0.0f) T = Tsat;
             float o0 = fmaf(T, bg0, C0), o1 = fmaf(T, bg1, C1), o2 = fmaf(T, bg2, C2);
             if (p.clamp01) {
                 o0 = fminf(fmaxf(o0, 0.0f), 1.0f);
@@ -128,7 +141,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             }
             if (p.final_T) p.final_T[(int64_t)f * hw + pix] = T;
             if (p.n_contrib) p.n_contrib[(int64_t)f * hw + pix] = last;
-            if (p.out_invdepth) p.out_invdepth[(int64_t)f * hw + pix] = Dv;
+            if (DEPTH) p.out_invdepth[(int64_t)f * hw + pix] = Dv;
         }
         __syncthreads();
     }
@@ -155,7 +168,8 @@ extern "C" int amav_splat_blend(const AmavSplatDims *d, const float *geom, const
     p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity; p.bg0 = p.bg1 = p.bg2 = 0.f;
     const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;
     const int grid = (int)(total_tiles < AMAV_SM_COUNT * 8 ? total_tiles : AMAV_SM_COUNT * 8);
-    blend_kernel<<<grid, BLEND_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
+    if (out_invdepth) blend_kernel<true><<<grid, BLEND_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
+    else blend_kernel<false><<<grid, BLEND_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }

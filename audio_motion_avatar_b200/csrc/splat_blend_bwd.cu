@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
                 const float4 bq = rec[1];
                 const float dx = a.x - pxf, dy = a.y - pyf;
                 const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (bq.x * dy) * dy);
-                bool use = (before + j + 1 <= last_contributor) && !(power > 0.0f) && !(power < bq.z);
+                bool use = (before + j + 1 <= last_contributor) && power <= 0.0f && !(power < bq.z);
                 float G = 0.0f, alpha = 0.0f;
                 if (use) {
                     G = amav_exp(power);

@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessParams 
                     // blend skips a pair before evaluating exp() when power < pmin: alpha = op*exp(power) is then
                     // below 1/255 with a 1e-4 relative margin, far above the rounding of logf/exp, so the exact
                     // alpha < 1/255 test that follows sees every borderline pair (bit-exact lists are kept).
-                    const float pmin = logf((1.0f / 255.0f) / op) - 1.0e-4f;
+                    const float pmin = fmaxf(logf((1.0f / 255.0f) / op) - 1.0e-4f, -80.0f);   // >= -80 (also for NaN): amav_exp's domain
                     g0 = make_float4(pix, piy, -0.5f * conx, -cony);
                     g1 = make_float4(-0.5f * conz, op, pmin, cr);
                     g2 = make_float4(cg, cb, pvz, (float)rad);

@@ -25,8 +25,8 @@
  *   - compiled with -ffp-contract=off: no implicit FMA contraction;
  *   - an FMA happens only where fmaf() is written;
  *   - expressions evaluate left to right exactly as written;
- *   - exp() in the blend is amav_exp() below (degree-7 polynomial, <= 1 ulp
- *     of expf over the range used).  Upstream uses CUDA expf (<= 2 ulp), which
+ *   - exp() in the blend is amav_exp() below (degree-5 minimax polynomial,
+ *     <= 1.5 ulp of exp over the range used).  Upstream uses CUDA expf (<= 2 ulp), which
  *     no CPU can reproduce bit for bit; define AMAV_ORACLE_LIBM_EXP to use
  *     libm expf instead (tests check the two agree to ~1e-7 relative).
  */
@@ -53,18 +53,15 @@ float amav_oracle_exp(float x)
     const float L2E_HI = 1.44269502162933349609375f;   /* fp32(log2 e)            */
     const float L2E_LO = 1.925963033500011e-8f;        /* log2 e - fp32(log2 e)   */
     const float MAGIC = 12582912.0f;                   /* 1.5 * 2^23              */
-    float t = x * L2E_HI;
-    float r = t + MAGIC;
-    float n = r - MAGIC;                               /* rint(t), exact          */
+    float r = fmaf(x, L2E_HI, MAGIC);
+    float n = r - MAGIC;                               /* rint(x log2 e), exact   */
     float f = fmaf(x, L2E_HI, -n);
     f = fmaf(x, L2E_LO, f);                            /* f in about [-0.5, 0.5]  */
-    float p = 1.5252733804059840e-5f;                  /* ln2^7/7!                */
-    p = fmaf(p, f, 1.5403530393381610e-4f);            /* ln2^6/6!                */
-    p = fmaf(p, f, 1.3333558146428443e-3f);            /* ln2^5/5!                */
-    p = fmaf(p, f, 9.6181291076284772e-3f);            /* ln2^4/4!                */
-    p = fmaf(p, f, 5.5504108664821580e-2f);            /* ln2^3/3!                */
-    p = fmaf(p, f, 2.4022650695910071e-1f);            /* ln2^2/2!                */
-    p = fmaf(p, f, 6.9314718055994531e-1f);            /* ln2                     */
+    float p = 0.001326472731307149f;                   /* degree-5 minimax of     */
+    p = fmaf(p, f, 0.009671512991189957f);             /* (2^f - 1)/f on          */
+    p = fmaf(p, f, 0.05550733581185341f);              /* [-0.5, 0.5]             */
+    p = fmaf(p, f, 0.24022242426872253f);
+    p = fmaf(p, f, 0.6931470036506653f);
     p = fmaf(p, f, 1.0f);
     int32_t ni = (int32_t)n;
     return u2f((uint32_t)((int32_t)f2u(p) + ni * (1 << 23)));
