@@ -67,6 +67,26 @@ __device__ __forceinline__ float amav_exp(float x, const ExpConsts ec)
     return __int_as_float(__float_as_int(p) + (ni << 23));
 }
 
+// Two independent amav_exp evaluations with their operations alternating, so that in-order issue overlaps the two
+// dependent chains (each result is bit-identical to amav_exp(x)).
+__device__ __forceinline__ void amav_exp_x2(float x0, float x1, const ExpConsts ec, float &e0, float &e1)
+{
+    const float L2E_HI = 1.44269502162933349609375f;
+    const float L2E_LO = 1.925963033500011e-8f;
+    const float MAGIC = 12582912.0f;
+    const float r0 = fmaf(x0, L2E_HI, ec.magic), r1 = fmaf(x1, L2E_HI, ec.magic);
+    const float n0 = r0 - MAGIC, n1 = r1 - MAGIC;
+    float f0 = fmaf(x0, L2E_HI, -n0), f1 = fmaf(x1, L2E_HI, -n1);
+    f0 = fmaf(x0, L2E_LO, f0); f1 = fmaf(x1, L2E_LO, f1);
+    float p0 = fmaf(ec.c5, f0, 0.009671512991189957f), p1 = fmaf(ec.c5, f1, 0.009671512991189957f);
+    p0 = fmaf(p0, f0, 0.05550733581185341f); p1 = fmaf(p1, f1, 0.05550733581185341f);
+    p0 = fmaf(p0, f0, 0.24022242426872253f); p1 = fmaf(p1, f1, 0.24022242426872253f);
+    p0 = fmaf(p0, f0, 0.6931470036506653f); p1 = fmaf(p1, f1, 0.6931470036506653f);
+    p0 = fmaf(p0, f0, 1.0f); p1 = fmaf(p1, f1, 1.0f);
+    e0 = __int_as_float(__float_as_int(p0) + ((__float_as_int(r0) - __float_as_int(MAGIC)) << 23));
+    e1 = __int_as_float(__float_as_int(p1) + ((__float_as_int(r1) - __float_as_int(MAGIC)) << 23));
+}
+
 // 16-byte shared-memory load at a 32-bit shared address + immediate offset.  The list walk addresses its records
 // as base + 48 j with the base held in a register; through a generic pointer ptxas rebuilds the shared window
 // base (S2R SR_CgaCtaId + LEA) for every entry.

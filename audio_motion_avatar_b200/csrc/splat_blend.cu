@@ -97,20 +97,23 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
                 cnt += __popc(m);
             }
             __syncwarp();
-            // 2. exact per-pixel blend over the warp's list (same arithmetic and tests as the oracle)
+            // 2. exact per-pixel blend over the warp's list (same arithmetic and tests as the oracle).  Two entries
+            // per iteration: alpha of both is computed branch-free (it does not depend on T, and 96% of the listed
+            // pairs need it on some lane anyway), so the two exp chains overlap; only the short T recurrence is serial.
+            // A deep tile is one CTA's sequential walk, and small launches last as long as their deepest tile.
             int last_off = -1;
-            for (int k = 0; k < cnt; ++k) {
-                const uint32_t off = list[k];
-                const uint32_t rec = rec_base + off;
+            auto pair_alpha = [&](uint32_t rec, float4 &b, float &alpha) -> bool {
                 const float4 a = lds128<0>(rec);
-                const float4 b = lds128<16>(rec);
+                b = lds128<16>(rec);
                 const float dx = a.x - pxf, dy = a.y - pyf;
                 const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (b.x * dy) * dy);
-                if (power > 0.0f || power < b.z) continue;              // b.z = pmin: alpha surely < 1/255
-                const float alpha = fminf(0.99f, b.y * amav_exp(power, ec));
-                if (alpha < alpha_min) continue;
+                alpha = fminf(0.99f, b.y * amav_exp(power, ec));
+                // b.z = pmin: alpha surely < 1/255 below it (and exp is only meaningful above it)
+                return !(power > 0.0f || power < b.z) && !(alpha < alpha_min);
+            };
+            auto accumulate = [&](uint32_t rec, uint32_t off, const float4 b, float alpha) {
                 const float Tn = T * (1.0f - alpha);
-                if (Tn < 0.0001f) { Tsat = fmaxf(Tsat, T); T = 0.0f; continue; }
+                if (Tn < 0.0001f) { Tsat = fmaxf(Tsat, T); T = 0.0f; return; }
                 const float w = alpha * T;
                 const float2 c = lds64<32>(rec);
                 C0 = fmaf(b.w, w, C0);
@@ -119,6 +122,29 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
                 if (DEPTH) Dv = fmaf(1.0f / lds64<40>(rec).x, w, Dv);
                 T = Tn;
                 last_off = (int)off;
+            };
+            int k = 0;
+            for (; k + 1 < cnt; k += 2) {
+                const uint32_t off0 = list[k], off1 = list[k + 1];
+                const uint32_t rec0 = rec_base + off0, rec1 = rec_base + off1;
+                const float4 a0 = lds128<0>(rec0), a1 = lds128<0>(rec1);
+                const float4 b0 = lds128<16>(rec0), b1 = lds128<16>(rec1);
+                const float dx0 = a0.x - pxf, dx1 = a1.x - pxf, dy0 = a0.y - pyf, dy1 = a1.y - pyf;
+                const float power0 = fmaf(fmaf(a0.w, dy0, a0.z * dx0), dx0, (b0.x * dy0) * dy0);
+                const float power1 = fmaf(fmaf(a1.w, dy1, a1.z * dx1), dx1, (b1.x * dy1) * dy1);
+                float e0, e1;
+                amav_exp_x2(power0, power1, ec, e0, e1);
+                const float alpha0 = fminf(0.99f, b0.y * e0), alpha1 = fminf(0.99f, b1.y * e1);
+                const bool ok0 = !(power0 > 0.0f || power0 < b0.z) && !(alpha0 < alpha_min);
+                const bool ok1 = !(power1 > 0.0f || power1 < b1.z) && !(alpha1 < alpha_min);
+                if (ok0) accumulate(rec0, off0, b0, alpha0);
+                if (ok1) accumulate(rec1, off1, b1, alpha1);
+            }
+            if (k < cnt) {
+                const uint32_t off0 = list[k];
+                float4 b0;
+                float alpha0;
+                if (pair_alpha(rec_base + off0, b0, alpha0)) accumulate(rec_base + off0, off0, b0, alpha0);
             }
             if (last_off >= 0) last = before + last_off / 48 + 1;
         }
