@@ -5,7 +5,7 @@ set -x
 O=gpurun_out
 SEQ="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline"
 TRN="python bench.py --workload train --steps 2 --warmup 3"
-OURS='regex:preprocess|scan_|scatter_entries|sort_tiles|blend|project|sample_decode|lbs_|pose_blend|skin|densify|chain_bwd'
+OURS='regex:preprocess|scan_|scatter_entries|sort_tiles|blend|project|sample_decode|lbs_|pose_blend|skin|densify|chain_bwd|image_loss'
 $SEQ > $O/ncu_seq_plain.json 2> $O/ncu_seq_plain.err || exit 1
 $TRN > $O/ncu_trn_plain.json 2> $O/ncu_trn_plain.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -k "$OURS" -c 400 --csv \
@@ -14,6 +14,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -k "$OURS" -c 400 --cs
     --log-file $O/launches_trn.csv $TRN > $O/ncu_trn.log 2>&1
 # full captures of the last (timed) step: sequence step = 14 library launches, 5 steps
 ncu --set full --clock-control none --import-source on -k "$OURS" --launch-skip 60 -c 14 -f -o $O/seq_full $SEQ > $O/ncu_seq_full.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:'::blend_bwd_kernel|::blend_kernel|sort_tiles' \
-    --launch-skip 24 -c 6 -f -o $O/trn_full $TRN > $O/ncu_trn_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k 'regex:^blend_bwd_kernel|^blend_kernel|sort_tiles|image_loss' \
+    --launch-skip 36 -c 12 -f -o $O/trn_full $TRN > $O/ncu_trn_full.log 2>&1
 ls -la $O
