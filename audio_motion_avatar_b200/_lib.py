@@ -37,9 +37,9 @@ _SIGS = {
     "amav_lbs_backward": [c_int, c_int, c_int, c_int] + [c_void_p] * 16 + [c_void_p],
     "amav_image_loss_forward": [c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
     "amav_image_loss_backward": [c_int, c_int, c_int] + [c_void_p] * 6 + [c_void_p],
-    "amav_splat_blend_backward": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_int64, c_void_p, c_int] + [c_void_p] * 5 + [c_void_p],
+    "amav_splat_blend_backward": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_int64, c_void_p, c_int] + [c_void_p] * 6 + [c_void_p],
     "amav_splat_preprocess_backward": [ctypes.POINTER(SplatDims)] + [c_void_p] * 15 + [c_void_p],
-    "amav_splat_blend": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_int64, c_void_p, c_int, c_int] + [c_void_p] * 5 + [c_void_p],
+    "amav_splat_blend": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_int64, c_void_p, c_int, c_int] + [c_void_p] * 6 + [c_void_p],
 }
 
 _lib = None
@@ -57,6 +57,8 @@ def lib() -> ctypes.CDLL:
         L.amav_launch_count.restype = c_int64
         L.amav_splat_scan_tmp_elems.restype = c_int64
         L.amav_splat_scan_tmp_elems.argtypes = [c_int64]
+        L.amav_splat_scan_order_offset.restype = c_int64
+        L.amav_splat_scan_order_offset.argtypes = [c_int64]
         for name, sig in _SIGS.items():
             if hasattr(L, name):
                 fn = getattr(L, name)

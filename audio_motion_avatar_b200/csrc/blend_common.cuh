@@ -103,6 +103,27 @@ template <int OFF> __device__ __forceinline__ float2 lds64(uint32_t addr)
     return v;
 }
 
+// Tile queue of the blend kernels.  A tile is one CTA's sequential walk and list lengths differ by orders of
+// magnitude, so a deep tile handed out late leaves the whole GPU waiting for one CTA (a 4-frame training launch
+// lasts exactly as long as its deepest tile).  amav_splat_scan lists the deep tiles (`order`: [0] = number with
+// >= AMAV_DEEP0 entries, stored from the front of the list; [1] = number with >= AMAV_DEEP1, stored from its back;
+// list of num_tiles words from [2]); the queue hands those out first, then every other tile in frame order.
+// Returns false when the queue is empty, else the tile in `t` or t = 0xffffffff for a position to skip (a deep
+// tile met again in the plain sweep).  Uniform across the CTA; `q` is the popped queue position.
+__device__ __forceinline__ bool queue_tile(unsigned int q, const uint32_t *__restrict__ order,
+                                           const uint32_t *__restrict__ tile_start, unsigned int total_tiles,
+                                           unsigned int &t)
+{
+    unsigned int nA = 0, nB = 0;
+    if (order) { nA = order[0]; nB = order[1]; }
+    if (q < nA) { t = order[2 + q]; return true; }
+    if (q < nA + nB) { t = order[2 + (total_tiles - 1 - (q - nA))]; return true; }
+    t = q - nA - nB;
+    if (t >= total_tiles) return false;
+    if (order && tile_start[t + 1] - tile_start[t] >= (uint32_t)AMAV_DEEP1) t = 0xffffffffu;
+    return true;
+}
+
 constexpr int BLEND_THREADS = 256;
 constexpr int SUB_W = 8, SUB_H = 4;        // pixels of one warp: 8 wide x 4 tall
 

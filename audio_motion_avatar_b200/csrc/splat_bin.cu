@@ -66,6 +66,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums(const uint32_t *
 // Single block: in-place exclusive scan of block_sums[0..nb); block_sums[nb] = grand total.
 __global__ void __launch_bounds__(SCAN_THREADS) scan_spine(uint32_t *block_sums, int nb)
 {
+    if (threadIdx.x == 0) { block_sums[nb + 1] = 0u; block_sums[nb + 2] = 0u; }      // deep-tile list counters
     uint32_t carry = 0;
     for (int base = 0; base < nb; base += SCAN_THREADS) {
         const int i = base + threadIdx.x;
@@ -80,7 +81,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_spine(uint32_t *block_sums,
 
 __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t *__restrict__ count, int64_t n,
                                                             const uint32_t *__restrict__ block_sums, int nb,
-                                                            uint32_t *__restrict__ start)
+                                                            uint32_t *__restrict__ start, uint32_t *__restrict__ order)
 {
     const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
     uint32_t c[SCAN_ITEMS];
@@ -96,6 +97,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t *__res
     for (int k = 0; k < SCAN_ITEMS; ++k) {
         if (base + k < n) start[base + k] = ex;
         ex += c[k];
+        // deep tiles, for the blend kernels' queues: >= AMAV_DEEP0 entries listed from the front, >= AMAV_DEEP1 from the back
+        if (c[k] >= (uint32_t)AMAV_DEEP0) order[2 + atomicAdd(order, 1u)] = (uint32_t)(base + k);
+        else if (c[k] >= (uint32_t)AMAV_DEEP1) order[2 + (n - 1 - atomicAdd(order + 1, 1u))] = (uint32_t)(base + k);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) start[n] = block_sums[nb];
 }
@@ -353,6 +357,11 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
 
 extern "C" int64_t amav_splat_scan_tmp_elems(int64_t num_tiles_total)
 {
+    return (num_tiles_total + SCAN_TILE - 1) / SCAN_TILE + 1 + 2 + num_tiles_total;
+}
+
+extern "C" int64_t amav_splat_scan_order_offset(int64_t num_tiles_total)
+{
     return (num_tiles_total + SCAN_TILE - 1) / SCAN_TILE + 1;
 }
 
@@ -369,7 +378,7 @@ extern "C" int amav_splat_scan(const AmavSplatDims *d, const uint32_t *tile_coun
     const int nb = amav_div_up(nt, SCAN_TILE);
     scan_block_sums<<<nb, SCAN_THREADS, 0, stream>>>(tile_count, nt, scan_tmp);
     scan_spine<<<1, SCAN_THREADS, 0, stream>>>(scan_tmp, nb);
-    scan_apply<<<nb, SCAN_THREADS, 0, stream>>>(tile_count, nt, scan_tmp, nb, tile_start);
+    scan_apply<<<nb, SCAN_THREADS, 0, stream>>>(tile_count, nt, scan_tmp, nb, tile_start, scan_tmp + nb + 1);
     amav_count_launches(2);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;

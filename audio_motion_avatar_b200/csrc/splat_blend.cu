@@ -18,6 +18,7 @@ struct BlendParams {
     int F, N, W, H, gx, gy, hwc, clamp01;
     const float4 *geom;
     const uint32_t *tile_start;
+    const uint32_t *order;            // deep-tile list of amav_splat_scan, or NULL
     const int32_t *point_list;
     float bg0, bg1, bg2;
     float *out_color, *final_T, *out_invdepth;
@@ -27,12 +28,12 @@ struct BlendParams {
 };
 
 template <bool DEPTH>
-__global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams p, const float *__restrict__ bg)
+__global__ void __launch_bounds__(BLEND_THREADS, 5) blend_kernel(const BlendParams p, const float *__restrict__ bg)
 {
     // one 48-byte record per staged entry: (x, y, -conic.x/2, -conic.y)(-conic.z/2, opacity, pmin, r)(g, b, depth, radius);
     // a single array so the list walk needs one address per entry (immediate offsets for the rest)
     __shared__ float4 s_rec[BLEND_THREADS * 3];
-    // per warp: byte offsets (48 j) of the batch entries that touch its rectangle
+    // per warp: shared addresses (record base + 48 j) of the batch entries that touch its rectangle
     __shared__ unsigned short s_list[BLEND_THREADS / 32][BLEND_THREADS];
     __shared__ unsigned int s_next;
     const int tiles = p.gx * p.gy;
@@ -43,10 +44,10 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
     const int lx = sx + (lane & (SUB_W - 1)), ly = sy + (lane >> 3);
     const float alpha_min = 1.0f / 255.0f;
     unsigned short *list = s_list[warp];
-    // the record base as a 32-bit shared address held in a register: the output of a volatile asm is not
-    // rematerialised (through a generic pointer ptxas rebuilds the shared window base, S2R + LEA, for every entry)
-    uint32_t rec_base;
-    asm volatile("mov.u32 %0, %1;" : "=r"(rec_base) : "r"((uint32_t)__cvta_generic_to_shared(s_rec)));
+    // the per-warp lists hold the records' shared-memory addresses (16 bits: static shared memory of a CTA that is
+    // not in a cluster starts at 0), so the list walk does no address arithmetic at all
+    const uint32_t rec_base = (uint32_t)__cvta_generic_to_shared(s_rec);
+    if (rec_base + 48u * BLEND_THREADS > 0x10000u) __trap();      // the lists hold 16-bit shared addresses
     __shared__ float s_expc[4];
     const ExpConsts ec = exp_consts(s_expc);
 
@@ -55,14 +56,17 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
         // tile from a device counter instead of striding, so no SM idles behind a column of deep tiles
         if (threadIdx.x == 0) s_next = atomicAdd(p.work_counter, 1u);
         __syncthreads();
-        const unsigned int t = s_next;
-        if (t >= total_tiles) break;
+        unsigned int t;
+        if (!queue_tile(s_next, p.order, p.tile_start, total_tiles, t)) break;
+        if (t == 0xffffffffu) { __syncthreads(); continue; }       // deep tile, already handed out
         const int f = (int)(t / tiles);
         const int tile = (int)(t - (unsigned int)f * tiles);
         const int ty = tile / p.gx, tx = tile - ty * p.gx;
         const int pxi = tx * 16 + lx, pyi = ty * 16 + ly;
         const bool inside = pxi < p.W && pyi < p.H;
-        const float pxf = (float)pxi, pyf = (float)pyi;
+        float pxf, pyf;                             // pinned: ptxas otherwise re-converts them inside the list walk
+        asm volatile("cvt.rn.f32.s32 %0, %1;" : "=f"(pxf) : "r"(pxi));
+        asm volatile("cvt.rn.f32.s32 %0, %1;" : "=f"(pyf) : "r"(pyi));
         const float rx0 = (float)(tx * 16 + sx), ry0 = (float)(ty * 16 + sy);
         // ranges are clamped to the caller's entry capacity: after a bucket overflow the frame is incomplete (the
         // overflow flag tells the host) but nothing is read out of bounds
@@ -93,7 +97,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
                 const int j = j0 + lane;
                 const bool keep = j < nb && warp_rect_keep(s_rec[3 * j], s_rec[3 * j + 1], rx0, ry0);
                 const unsigned int m = __ballot_sync(0xffffffffu, keep);
-                if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(48 * j);
+                if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(rec_base + 48u * (uint32_t)j);
                 cnt += __popc(m);
             }
             __syncwarp();
@@ -126,7 +130,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
             int k = 0;
             for (; k + 1 < cnt; k += 2) {
                 const uint32_t off0 = list[k], off1 = list[k + 1];
-                const uint32_t rec0 = rec_base + off0, rec1 = rec_base + off1;
+                const uint32_t rec0 = off0, rec1 = off1;
                 const float4 a0 = lds128<0>(rec0), a1 = lds128<0>(rec1);
                 const float4 b0 = lds128<16>(rec0), b1 = lds128<16>(rec1);
                 const float dx0 = a0.x - pxf, dx1 = a1.x - pxf, dy0 = a0.y - pyf, dy1 = a1.y - pyf;
@@ -144,9 +148,9 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
                 const uint32_t off0 = list[k];
                 float4 b0;
                 float alpha0;
-                if (pair_alpha(rec_base + off0, b0, alpha0)) accumulate(rec_base + off0, off0, b0, alpha0);
+                if (pair_alpha(off0, b0, alpha0)) accumulate(off0, off0, b0, alpha0);
             }
-            if (last_off >= 0) last = before + last_off / 48 + 1;
+            if (last_off >= 0) last = before + (last_off - (int)rec_base) / 48 + 1;
         }
         if (inside) {
             if (T == 0.0f) T = Tsat;
@@ -178,7 +182,7 @@ __global__ void __launch_bounds__(BLEND_THREADS) blend_kernel(const BlendParams 
 extern "C" int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
                                 const int32_t *point_list, int64_t capacity, const float *bg, int hwc, int clamp01,
                                 float *out_color, float *final_T, int32_t *n_contrib, float *out_invdepth,
-                                uint32_t *work_counter, void *stream)
+                                uint32_t *work_counter, const uint32_t *tile_order, void *stream)
 {
     AMAV_CHECK_ARG(d && d->frames >= 0 && d->width > 0 && d->height > 0, "bad dims");
     if (d->frames == 0) return AMAV_OK;
@@ -189,7 +193,7 @@ extern "C" int amav_splat_blend(const AmavSplatDims *d, const float *geom, const
     p.gx = (d->width + 15) / 16; p.gy = (d->height + 15) / 16; p.hwc = hwc; p.clamp01 = clamp01;
     p.geom = reinterpret_cast<const float4 *>(geom); p.tile_start = tile_start; p.point_list = point_list;
     p.out_color = out_color; p.final_T = final_T; p.n_contrib = n_contrib; p.out_invdepth = out_invdepth;
-    p.work_counter = work_counter;
+    p.work_counter = work_counter; p.order = d->frames <= AMAV_DEEP_FIRST_MAX_FRAMES ? tile_order : nullptr;
     AMAV_CHECK_ARG(capacity >= 0, "bad capacity");
     p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity; p.bg0 = p.bg1 = p.bg2 = 0.f;
     const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;

@@ -23,6 +23,7 @@ struct BlendBwdParams {
     int F, N, W, H, gx, gy, hwc;
     const float4 *geom;
     const uint32_t *tile_start;
+    const uint32_t *order;            // deep-tile list of amav_splat_scan, or NULL
     const int32_t *point_list;
     const float *final_T;
     const int32_t *n_contrib;
@@ -67,8 +68,9 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
     for (;;) {
         if (threadIdx.x == 0) { s_next = atomicAdd(p.work_counter, 1u); s_maxc = 0; }
         __syncthreads();
-        const unsigned int t = s_next;
-        if (t >= total_tiles) break;
+        unsigned int t;
+        if (!queue_tile(s_next, p.order, p.tile_start, total_tiles, t)) break;
+        if (t == 0xffffffffu) { __syncthreads(); continue; }       // deep tile, already handed out
         const int f = (int)(t / tiles);
         const int tile = (int)(t - (unsigned int)f * tiles);
         const int ty = tile / p.gx, tx = tile - ty * p.gx;
@@ -242,7 +244,7 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
 extern "C" int amav_splat_blend_backward(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
                                          const int32_t *point_list, int64_t capacity, const float *bg, int hwc,
                                          const float *final_T, const int32_t *n_contrib, const float *dL_dcolor,
-                                         float *dsum, uint32_t *work_counter, void *stream)
+                                         float *dsum, uint32_t *work_counter, const uint32_t *tile_order, void *stream)
 {
     AMAV_CHECK_ARG(d && d->frames >= 0 && d->width > 0 && d->height > 0, "bad dims");
     if (d->frames == 0) return AMAV_OK;
@@ -254,7 +256,7 @@ extern "C" int amav_splat_blend_backward(const AmavSplatDims *d, const float *ge
     p.gx = (d->width + 15) / 16; p.gy = (d->height + 15) / 16; p.hwc = hwc;
     p.geom = reinterpret_cast<const float4 *>(geom); p.tile_start = tile_start; p.point_list = point_list;
     p.final_T = final_T; p.n_contrib = n_contrib; p.dL_dpix = dL_dcolor; p.dsum = dsum;
-    p.work_counter = work_counter;
+    p.work_counter = work_counter; p.order = d->frames <= AMAV_DEEP_FIRST_MAX_FRAMES ? tile_order : nullptr;
     p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity;
     const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;
     AMAV_CHECK_ARG(total_tiles < ((int64_t)1 << 31), "too many tiles");

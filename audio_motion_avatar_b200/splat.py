@@ -95,6 +95,7 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     work_counter = counters[2 * nt + 2:2 * nt + 3]
     tile_start = ws.get("tile_start", nt + 1, torch.int32, dev)
     scan_tmp = ws.get("scan_tmp", int(_lib.lib().amav_splat_scan_tmp_elems(nt)), torch.int32, dev)
+    tile_order = scan_tmp[int(_lib.lib().amav_splat_scan_order_offset(nt)):]      # deep tiles first (written by the scan)
     ws.overflow = overflow[:1]
 
     call("amav_splat_preprocess", dims, ptr(means3d), ptr(scales), ptr(rots), ptr(opacities), ptr(colors),
@@ -118,8 +119,8 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     n_contrib = torch.empty(F, height, width, dtype=torch.int32, device=dev) if want_aux else None
     invdepth = torch.empty(F, 1, height, width, dtype=torch.float32, device=dev) if want_invdepth else None
     call("amav_splat_blend", dims, ptr(geom), ptr(tile_start), ptr(ws.point_list), ws.capacity, ptr(bg), int(hwc), int(clamp01),
-         ptr(out), ptr(final_T), ptr(n_contrib), ptr(invdepth), ptr(work_counter), st)
-    return {"color": out, "geom": geom.view(F, N, 12), "rect": rect.view(F, N, 4), "tiles_touched": touched.view(F, N),
+         ptr(out), ptr(final_T), ptr(n_contrib), ptr(invdepth), ptr(work_counter), ptr(tile_order), st)
+    return {"color": out, "tile_order": tile_order, "geom": geom.view(F, N, 12), "rect": rect.view(F, N, 4), "tiles_touched": touched.view(F, N),
             "tile_start": tile_start, "point_list": ws.point_list, "D": D, "final_T": final_T,
             "n_contrib": n_contrib, "invdepth": invdepth, "workspace": ws}
 
@@ -145,7 +146,7 @@ def splat_backward(fwd: Dict[str, torch.Tensor], grad_color: torch.Tensor, means
     ws = fwd["workspace"]
     geom = fwd["geom"].reshape(-1)
     call("amav_splat_blend_backward", dims, ptr(geom), ptr(fwd["tile_start"]), ptr(fwd["point_list"]), ws.capacity,
-         ptr(bg), int(hwc), ptr(fwd["final_T"]), ptr(fwd["n_contrib"]), ptr(grad_color), ptr(dsum), ptr(counter), st)
+         ptr(bg), int(hwc), ptr(fwd["final_T"]), ptr(fwd["n_contrib"]), ptr(grad_color), ptr(dsum), ptr(counter), ptr(fwd.get("tile_order")), st)
     d_means = torch.empty(G, N, 3, device=dev)
     d_scales = torch.empty(G, N, 3, device=dev)
     d_rots = torch.empty(G, N, 4, device=dev)

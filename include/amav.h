@@ -126,13 +126,17 @@ int amav_splat_preprocess(const AmavSplatDims *d, const float *means3d, const fl
  *     Together equivalent to upstream's InclusiveSum + duplicateWithKeys + SortPairs +
  *     identifyTileRanges: tile t's sorted run is point_list[tile_start[t] : tile_start[t+1]], ordered
  *     by (depth bits, Gaussian index) = a stable sort of (tile<<32 | depth) keys.
- *   scan_tmp   [amav_splat_scan_tmp_elems(F*tiles)] uint32 scratch
+ *   scan_tmp   [amav_splat_scan_tmp_elems(F*tiles)] uint32 scratch.  From element amav_splat_scan_order_offset(F*tiles)
+ *              on it holds the deep-tile list the blend kernels take as `tile_order`: [0] = number of tiles with
+ *              >= 4096 entries (listed from the front), [1] = number with 2048..4095 (listed from the back), then
+ *              F*tiles words of list.  Valid until the next amav_splat_scan on the same scratch.
  *   tile_cursor[F*tiles] uint32: MUST be zeroed by the caller (scratch: bucket cursors, then the large-bucket sort's queue head)
  *   entries    [capacity] uint64 scratch; point_list [capacity] int32 out (Gaussian index within the frame)
  *   overflow   [2] int32, MUST be zeroed by the caller: [0] is set to 1 (and binning truncated) when D > capacity;
  *              [1] is the sort kernel's tile queue head
  */
 int64_t amav_splat_scan_tmp_elems(int64_t num_tiles_total);
+int64_t amav_splat_scan_order_offset(int64_t num_tiles_total);
 int amav_splat_scan(const AmavSplatDims *d, const uint32_t *tile_count, uint32_t *tile_start,
                     uint32_t *scan_tmp, void *stream);
 int amav_splat_bin(const AmavSplatDims *d, const float *geom, const uint16_t *rect,
@@ -145,11 +149,14 @@ int amav_splat_bin(const AmavSplatDims *d, const float *geom, const uint16_t *re
  *   final_T [F,H,W], n_contrib [F,H,W] int32, out_invdepth [F,H,W]: each may be NULL (inference).
  *   capacity: entries in point_list (same value as given to amav_splat_bin); tile ranges are clamped to it.
  *   work_counter [1] uint32: MUST be zeroed by the caller (tiles are handed to CTAs dynamically).
+ *   tile_order: the deep-tile list written by amav_splat_scan (see scan_tmp), or NULL for plain frame order.  A tile
+ *   is one CTA's sequential walk, so the deepest tiles go first (in launches of up to 32 frames, where the tail
+ *   matters); the result does not depend on the order.
  */
 int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
                      const int32_t *point_list, int64_t capacity, const float *bg, int hwc, int clamp01,
                      float *out_color, float *final_T, int32_t *n_contrib, float *out_invdepth,
-                     uint32_t *work_counter, void *stream);
+                     uint32_t *work_counter, const uint32_t *tile_order, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Stage 4 backward (diff_gaussian_rasterization's _RasterizeGaussians.backward, reached in the reference
@@ -162,7 +169,7 @@ int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *
  *   dsum      [F,N,12] fp32, MUST be zeroed by the caller, 16-byte aligned:
  *             0,1 dL/dmean2D (x 0.5*W, 0.5*H as upstream), 2..4 dL/dconic (A, B, C; B holds half the true
  *             derivative, upstream's convention), 5 dL/dopacity, 6..8 dL/drgb, 9..11 unused
- *   work_counter [1] uint32: MUST be zeroed by the caller.
+ *   work_counter [1] uint32: MUST be zeroed by the caller; tile_order as in amav_splat_blend (or NULL).
  * amav_splat_preprocess_backward: sums -> gradients of the rasteriser inputs, through render_one's activations when
  *   d->activate (renderer.py:532-533,547), summed over the views_per_set views that share a Gaussian set.
  *   d_means3d/d_scales/d_colors [G,N,3], d_rots [G,N,4] (16-byte aligned), d_opacities [G,N], G = F/views_per_set.
@@ -170,7 +177,7 @@ int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *
 int amav_splat_blend_backward(const AmavSplatDims *d, const float *geom, const uint32_t *tile_start,
                               const int32_t *point_list, int64_t capacity, const float *bg, int hwc,
                               const float *final_T, const int32_t *n_contrib, const float *dL_dcolor,
-                              float *dsum, uint32_t *work_counter, void *stream);
+                              float *dsum, uint32_t *work_counter, const uint32_t *tile_order, void *stream);
 int amav_splat_preprocess_backward(const AmavSplatDims *d, const float *means3d, const float *scales,
                                    const float *rots, const float *opacities, const float *colors,
                                    const float *view, const float *proj, const float *tanfov,
