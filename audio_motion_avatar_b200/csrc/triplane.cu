@@ -133,11 +133,12 @@ __global__ void __launch_bounds__(256) sample_decode_kernel(const SampleParams p
                                                   p.weight[(int64_t)row * p.ldw + 2], p.bias[row]);
     }
     __syncthreads();
-    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t gid = tid >> 2;
-    const int lane4 = (int)(tid & 3);
-    if (gid >= (int64_t)p.F * p.N) return;
-    const int f = (int)(gid / p.N);
+    // grid = (site groups, frames): no 64-bit division to find the frame
+    const int f = blockIdx.y;
+    const int site = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 2);
+    const int lane4 = (int)(threadIdx.x & 3);
+    if (site >= p.N) return;
+    const int64_t gid = (int64_t)f * p.N + site;
     const float px = p.points[3 * gid], py = p.points[3 * gid + 1], pz = p.points[3 * gid + 2];
     const float gx = fminf(fmaxf(px / p.radius, -1.0f), 1.0f);
     const float gy = fminf(fmaxf(py / p.radius, -1.0f), 1.0f);
@@ -153,21 +154,21 @@ __global__ void __launch_bounds__(256) sample_decode_kernel(const SampleParams p
         float wx1, wy1;
         tap_coords(ua[pl], R, x0, wx1);
         tap_coords(va[pl], R, y0, wy1);
-        const float wx0 = 1.0f - wx1, wy0 = 1.0f - wy1;
-        const float4 *plane = base + (int64_t)pl * R2 * 4;
-        float4 pacc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int dy = 0; dy < 2; ++dy)
-#pragma unroll
-            for (int dx = 0; dx < 2; ++dx) {
-                const int xi = x0 + dx, yi = y0 + dy;
-                if (xi >= 0 && xi < R && yi >= 0 && yi < R) {
-                    const float w = (dx ? wx1 : wx0) * (dy ? wy1 : wy0);
-                    const float4 t = __ldg(plane + (int64_t)(yi * R + xi) * 4);
-                    pacc.x = fmaf(t.x, w, pacc.x); pacc.y = fmaf(t.y, w, pacc.y);
-                    pacc.z = fmaf(t.z, w, pacc.z); pacc.w = fmaf(t.w, w, pacc.w);
-                }
-            }
+        // zero padding without branches: an out-of-range tap (index -1 or R) gets weight 0 and a clamped address
+        const float wx0 = x0 >= 0 ? 1.0f - wx1 : 0.0f, wy0 = y0 >= 0 ? 1.0f - wy1 : 0.0f;
+        wx1 = x0 + 1 < R ? wx1 : 0.0f;
+        wy1 = y0 + 1 < R ? wy1 : 0.0f;
+        const int xa = max(x0, 0), xb = min(x0 + 1, R - 1), ya = max(y0, 0) * R, yb = min(y0 + 1, R - 1) * R;
+        const float4 *plane = base + pl * R2 * 4;
+        const float4 t00 = __ldg(plane + (ya + xa) * 4), t01 = __ldg(plane + (ya + xb) * 4);
+        const float4 t10 = __ldg(plane + (yb + xa) * 4), t11 = __ldg(plane + (yb + xb) * 4);
+        const float w00 = wx0 * wy0, w01 = wx1 * wy0, w10 = wx0 * wy1, w11 = wx1 * wy1;
+        // same accumulation order as before: (y0,x0), (y0,x1), (y1,x0), (y1,x1)
+        float4 pacc;
+        pacc.x = fmaf(t11.x, w11, fmaf(t10.x, w10, fmaf(t01.x, w01, t00.x * w00)));
+        pacc.y = fmaf(t11.y, w11, fmaf(t10.y, w10, fmaf(t01.y, w01, t00.y * w00)));
+        pacc.z = fmaf(t11.z, w11, fmaf(t10.z, w10, fmaf(t01.z, w01, t00.z * w00)));
+        pacc.w = fmaf(t11.w, w11, fmaf(t10.w, w10, fmaf(t01.w, w01, t00.w * w00)));
         acc.x += pacc.x; acc.y += pacc.y; acc.z += pacc.z; acc.w += pacc.w;
     }
     // xyz columns of the heads + bias (x = [points, feats], renderer.py:165)
@@ -179,7 +180,8 @@ __global__ void __launch_bounds__(256) sample_decode_kernel(const SampleParams p
     }
     if (lane4 == 0) {                      // rot = normalize(rotation), eps 1e-12 (renderer.py:333)
         const float n = fmaxf(sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3]), 1e-12f);
-        reinterpret_cast<float4 *>(p.rot)[gid] = make_float4(v[0] / n, v[1] / n, v[2] / n, v[3] / n);
+        const float inv = 1.0f / n;        // one division; x * (1/n) is within 1 ulp of x / n
+        reinterpret_cast<float4 *>(p.rot)[gid] = make_float4(v[0] * inv, v[1] * inv, v[2] * inv, v[3] * inv);
     } else if (lane4 == 1) {               // xyz = points + offset + transl (renderer.py:338); opacity raw
         const float *t = p.transl + 3 * f;
         p.xyz[3 * gid] = px + v[0] + t[0];
@@ -188,10 +190,10 @@ __global__ void __launch_bounds__(256) sample_decode_kernel(const SampleParams p
         p.opacity[gid] = v[3];
     } else if (lane4 == 2) {               // scale raw
         p.scale[3 * gid] = v[0]; p.scale[3 * gid + 1] = v[1]; p.scale[3 * gid + 2] = v[2];
-    } else {                               // color = sigmoid(shs) (renderer.py:335)
-        p.color[3 * gid] = 1.0f / (1.0f + expf(-v[0]));
-        p.color[3 * gid + 1] = 1.0f / (1.0f + expf(-v[1]));
-        p.color[3 * gid + 2] = 1.0f / (1.0f + expf(-v[2]));
+    } else {                               // color = sigmoid(shs) (renderer.py:335); 1 + e^-v in [1, inf): fast divide
+        p.color[3 * gid] = __fdividef(1.0f, 1.0f + expf(-v[0]));
+        p.color[3 * gid + 1] = __fdividef(1.0f, 1.0f + expf(-v[1]));
+        p.color[3 * gid + 2] = __fdividef(1.0f, 1.0f + expf(-v[2]));
     }
 }
 
@@ -232,8 +234,8 @@ extern "C" int amav_sample_decode(int F, int N, int C, int R, float radius, cons
     p.proj = reinterpret_cast<const float4 *>(proj); p.points = points; p.transl = transl;
     p.weight = weight; p.bias = bias; p.ldw = 3 + 3 * C;
     p.xyz = xyz; p.scale = scale; p.rot = rot; p.opacity = opacity; p.color = color;
-    const int64_t threads = (int64_t)F * N * 4;
-    sample_decode_kernel<<<amav_div_up(threads, 256), 256, 0, stream>>>(p);
+    AMAV_CHECK_ARG(F <= 65535 && (int64_t)3 * R * R * 4 < ((int64_t)1 << 31), "too many frames / planes too large for one call");
+    sample_decode_kernel<<<dim3(amav_div_up((int64_t)N * 4, 256), F), 256, 0, stream>>>(p);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }
