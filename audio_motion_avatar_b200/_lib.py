@@ -5,7 +5,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_float, c_int, c_int32, c_int64, c_void_p
+from ctypes import c_double, c_float, c_int, c_int32, c_int64, c_void_p
 
 import torch
 
@@ -35,6 +35,7 @@ _SIGS = {
     "amav_triplane_project_backward": [c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p],
     "amav_densify_gather_backward": [c_int, c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
     "amav_lbs_backward": [c_int, c_int, c_int, c_int] + [c_void_p] * 16 + [c_void_p],
+    "amav_camera_setup": [c_int, c_void_p, c_void_p, c_int, c_int, c_double, c_double, c_void_p, c_void_p, c_void_p, c_void_p],
     "amav_image_loss_forward": [c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
     "amav_image_loss_backward": [c_int, c_int, c_int] + [c_void_p] * 6 + [c_void_p],
     "amav_splat_blend_backward": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_int64, c_void_p, c_int] + [c_void_p] * 6 + [c_void_p],

@@ -24,6 +24,7 @@ SOURCES = [
     ("lbs.cu", []),
     ("lbs_bwd.cu", []),
     ("image_loss.cu", []),
+    ("camera.cu", ["-fmad=false"]),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
           "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]

@@ -43,35 +43,24 @@ def camera_matrices(K: torch.Tensor, E: torch.Tensor, height: int, width: int):
     """K [F,3,3], E [F,4,4] on the device -> (viewmatrix [F,4,4], projmatrix [F,4,4], tanfov [F,2]) exactly as
     render_one hands them to GaussianRasterizationSettings (already transposed), without a host sync.
 
-    The reference builds Rt = E, inverts it twice (getWorld2View2_torch), forms K_ndc from Python floats
-    (double precision) and takes math.tan of the fp32 half-angle in double; the same operations are done
-    here batched: two ``torch.linalg.inv``, double arithmetic for K_ndc and tan, then a cast to fp32."""
-    K = K.reshape(-1, 3, 3).float()
-    E = E.reshape(-1, 4, 4).float()
-    Fr = K.shape[0]
+    One launch of ``amav_camera_setup`` for all frames (csrc/camera.cu): Rt from the extrinsic (the reference's two
+    fp32 inversions of it cancel up to ~1e-7 of rounding noise), K_ndc and tan of the half-angle in double as the
+    reference's Python floats / math.tan, view x proj in fp32."""
+    K = K.reshape(-1, 3, 3).to(torch.float32).contiguous()
+    E = E.reshape(-1, 4, 4).to(torch.float32).contiguous()
+    Fr = int(K.shape[0])
+    if E.shape[0] != Fr:
+        raise ValueError("K and E differ in frame count")
     dev = K.device
-    Rt = torch.zeros(Fr, 4, 4, device=dev)
-    Rt[:, :3, :3] = E[:, :3, :3]
-    Rt[:, :3, 3] = E[:, :3, 3]
-    Rt[:, 3, 3] = 1.0
-    # inv_ex: same LU-based inverse as torch.inverse, without the host read of the `info` flag (a device sync)
-    view = torch.linalg.inv_ex(torch.linalg.inv_ex(Rt).inverse).inverse.transpose(1, 2)
-    fx, fy, cx, cy = K[:, 0, 0], K[:, 1, 1], K[:, 0, 2], K[:, 1, 2]
-    fovx = 2 * torch.atan(width / (2 * fx))
-    fovy = 2 * torch.atan(height / (2 * fy))
-    tanfov = torch.stack([torch.tan((fovx * 0.5).double()), torch.tan((fovy * 0.5).double())], dim=1).float()
-    fxd, fyd, cxd, cyd = fx.double(), fy.double(), cx.double(), cy.double()
-    Kn = torch.zeros(Fr, 4, 4, dtype=torch.float64, device=dev)
-    Kn[:, 0, 0] = 2 * fxd / width
-    Kn[:, 0, 2] = (2 * cxd - width) / width
-    Kn[:, 1, 1] = 2 * fyd / height
-    Kn[:, 1, 2] = (2 * cyd - height) / height
-    Kn[:, 2, 2] = ZFAR / (ZFAR - ZNEAR)
-    Kn[:, 2, 3] = -ZFAR * ZNEAR / (ZFAR - ZNEAR)
-    Kn[:, 3, 2] = 1.0
-    proj = Kn.float().transpose(1, 2)
-    full = torch.bmm(view, proj)
-    return view.contiguous(), full.contiguous(), tanfov.contiguous()
+    view = torch.empty(Fr, 4, 4, device=dev)
+    full = torch.empty(Fr, 4, 4, device=dev)
+    tanfov = torch.empty(Fr, 2, device=dev)
+    _lib.call("amav_camera_setup", Fr, _lib.ptr(K), _lib.ptr(E), int(width), int(height), ZNEAR, ZFAR,
+              _lib.ptr(view), _lib.ptr(full), _lib.ptr(tanfov), _lib.stream_ptr())
+    return view, full, tanfov
+
+
+_BG_CACHE: Dict[tuple, torch.Tensor] = {}
 
 
 def _background(bg_color, device) -> torch.Tensor:
@@ -79,7 +68,11 @@ def _background(bg_color, device) -> torch.Tensor:
         bg_color = [1, 1, 1]
     if isinstance(bg_color, torch.Tensor):
         return bg_color.to(device, torch.float32).reshape(3)
-    return torch.tensor(list(bg_color), dtype=torch.float32, device=device)
+    key = (str(device), tuple(float(c) for c in bg_color))
+    t = _BG_CACHE.get(key)                      # a Python-list background is uploaded once per device, not per call
+    if t is None:
+        t = _BG_CACHE[key] = torch.tensor(list(key[1]), dtype=torch.float32, device=device)
+    return t
 
 
 _WORKSPACES: Dict[int, SplatWorkspace] = {}

@@ -164,6 +164,10 @@ def stage_bytes(name, Fr, N, V, J, S, P, H, W, D):
         return const + Fr * (4 * V * 12 + J * 48 * 2)
     if name == "amav_densify_gather_backward":
         return N * P * 8 + Fr * (V * 12 + N * 12)
+    if name == "amav_camera_setup":
+        return Fr * (36 + 64 + 64 + 64 + 8)
+    if name in ("amav_image_loss_forward", "amav_image_loss_backward"):
+        return Fr * H * W * 3 * 4 * (2 + 3) + (Fr * H * W * 12 if name.endswith("backward") else 0)
     return 0
 
 

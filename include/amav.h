@@ -158,6 +158,14 @@ int amav_splat_blend(const AmavSplatDims *d, const float *geom, const uint32_t *
                      float *out_color, float *final_T, int32_t *n_contrib, float *out_invdepth,
                      uint32_t *work_counter, const uint32_t *tile_order, void *stream);
 
+/* Camera set-up of render_one for F frames (renderer.py:486-510; graphic_utils.py:67-78,103-136,144-145):
+ *   K [F,3,3] intrinsics, E [F,4,4] world-to-camera extrinsics ->
+ *   view [F,4,4] = getWorld2View2_torch(R, T)^T, full [F,4,4] = view x getProjectionMatrix_torch(...)^T (the two
+ *   matrices GaussianRasterizationSettings takes, already transposed), tanfov [F,2] = tan(fov/2) of focal2fov_torch.
+ *   The reference's double fp32 inversion of Rt is replaced by Rt itself (~1e-7 relative difference). */
+int amav_camera_setup(int F, const float *K, const float *E, int width, int height, double znear, double zfar,
+                      float *view, float *full, float *tanfov, void *stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Stage 4 backward (diff_gaussian_rasterization's _RasterizeGaussians.backward, reached in the reference
  * through autograd from renderer.py:555-568).  Needs the forward's geom, tile_start,
