@@ -86,6 +86,32 @@ def _workspace(device) -> SplatWorkspace:
     return ws
 
 
+_DEFERRED: Optional[list] = None
+
+
+class deferred_overflow_checks:
+    """``with deferred_overflow_checks() as chk:`` -- inference calls inside the block do not read their bucket
+    overflow flag back (one host sync per call, which also keeps the CPU from enqueueing the next call's kernels
+    while this one renders); ``chk.overflowed()`` reads all of them at once afterwards.  If it returns True the
+    frames of the block are incomplete: render them again outside the block (the sizing read then grows the buffers).
+    Used where one logical render is cut into pieces (``shard.render_and_gather``)."""
+
+    def __enter__(self):
+        global _DEFERRED
+        self._prev, _DEFERRED = _DEFERRED, []
+        self._flags = _DEFERRED
+        return self
+
+    def __exit__(self, *exc):
+        global _DEFERRED
+        _DEFERRED = self._prev
+
+    def overflowed(self) -> bool:
+        if not self._flags:
+            return False
+        return bool(torch.stack([f.reshape(()) for f in self._flags]).any().item())
+
+
 def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug, views_per_set, hwc,
                    out=None, defer_check=False, cameras=None):
     """All frames of a call in one batched splat pass.  Gaussian tensors [G,N,k] (pre-activation scale and
@@ -124,18 +150,22 @@ def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug,
                              workspace=ws, sync_free=sync_free, out=out)
 
     res = run(sync_free=ws.capacity > 0)
-    if res["D"] < 0 and not defer_check:
+    if res["D"] < 0 and not defer_check and _DEFERRED is not None:
+        _DEFERRED.append(ws.overflow.clone())           # the flag buffer is reused (zeroed) by the next call
+    elif res["D"] < 0 and not defer_check:
         if int(ws.overflow.item()) != 0:
             res = run(sync_free=False)
     return res["color"]
 
 
-def render_batch(gaussians, K, E, args, bg_color=None, debug=False):
-    """renderer.py:447-479.  gaussians: dict of [B*T,N,k]; K [B,T,3,3]; E [B,T,4,4] -> [B,T,H,W,3] in [0,1]."""
+def render_batch(gaussians, K, E, args, bg_color=None, debug=False, out=None):
+    """renderer.py:447-479.  gaussians: dict of [B*T,N,k]; K [B,T,3,3]; E [B,T,4,4] -> [B,T,H,W,3] in [0,1].
+    ``out`` (inference only): a contiguous [B*T,H,W,3] fp32 device buffer the frames are written into -- it may be
+    another GPU's memory mapped into this process (``shard.PeerFrameGather``)."""
     B, T = E.shape[0], E.shape[1]
     g = lambda k, d: gaussians[k].reshape(B * T, -1, d).float()
     img = _render_frames(g("xyz", 3), g("rot", 4), g("scale", 3), g("opacity", 1), g("color", 3),
-                         K.reshape(-1, 3, 3), E.reshape(-1, 4, 4), args, bg_color, debug, 1, True)
+                         K.reshape(-1, 3, 3), E.reshape(-1, 4, 4), args, bg_color, debug, 1, True, out=out)
     return img.reshape(B, T, int(args.image_size[0]), int(args.image_size[1]), 3)
 
 
@@ -327,9 +357,10 @@ class Renderer(nn.Module):
         proj = stages.triplane_project(triplane_features, W, C, R)
         return stages.sample_decode(proj, points, transl, W, b, C, R, float(self.cfg.radius))
 
-    def forward(self, triplane_features, cam_params, smpl_tokens=None, smpl_params_gt=None):
+    def forward(self, triplane_features, cam_params, smpl_tokens=None, smpl_params_gt=None, out=None):
         """renderer.py:73-204.  triplane_features [B,T,C,3*R*R]; cam_params {'intrinsic' [B,T,3,3], 'extrinsic'
-        [B,T,4,4]}; returns (rendered_images [B,T,H,W,3], gaussians[, pred_smpl_params])."""
+        [B,T,4,4]}; returns (rendered_images [B,T,H,W,3], gaussians[, pred_smpl_params]).  ``out`` (extension,
+        inference only): [B*T,H,W,3] buffer to render into, see ``render_batch``."""
         dev = self._device
         if smpl_tokens is not None:
             B, T = smpl_tokens.shape[0], smpl_tokens.shape[1]
@@ -357,7 +388,7 @@ class Renderer(nn.Module):
         points = self.get_smpl_vertices(smpl_params)                                   # [F,N,3]
         transl = smpl_params["transl"].reshape(B * T, 3).to(dev, torch.float32)
         gaussians = self.decode_gaussians(tokens, points, transl)
-        rendered = render_batch(gaussians, cam_params["intrinsic"], cam_params["extrinsic"], self.cfg, debug=False)
+        rendered = render_batch(gaussians, cam_params["intrinsic"], cam_params["extrinsic"], self.cfg, debug=False, out=out)
         if getattr(self.cfg, "predict_smplx_params", False):
             return rendered, gaussians, pred_smpl_params
         return rendered, gaussians

@@ -49,6 +49,112 @@ def gather_frames(local: torch.Tensor, num_frames: int, dst: int = 0, group=None
     return out
 
 
+def chunk_bounds(size: int, chunks: int) -> List[int]:
+    """chunks + 1 boundaries cutting ``size`` frames into near-equal pieces, the larger (and, for size < chunks, the
+    non-empty) ones first (same rule on every rank)."""
+    chunks = max(1, int(chunks))
+    return [(i * size + chunks - 1) // chunks for i in range(chunks + 1)]
+
+
+def render_and_gather(render, tokens: torch.Tensor, cams: dict, params: dict, num_frames: int, chunks: int = 4,
+                      dst: int = 0, group=None, out: Optional[torch.Tensor] = None,
+                      defer=None) -> Optional[torch.Tensor]:
+    """Render this rank's shard ([1, f_r, ...] inputs as ``shard_inputs`` cuts them) in ``chunks`` pieces and gather
+    the frames on ``dst`` while the next piece renders: ``render(tokens, cams, None, params)`` is ``Renderer.forward``.
+
+    The gather is what limits scaling when it runs after the render: ``dst`` takes in (world - 1) x f_r frames over
+    one NVLink port (900 GB/s), 10.6 GB = 12 ms for 8 x 120 frames of 1024^2 next to an 18 ms render.  Posting the
+    send of piece k as soon as it is enqueued lets NCCL's stream move it while the main stream renders piece k+1,
+    which leaves only the last piece's transfer exposed.  ``defer``: ``renderer.deferred_overflow_checks`` -- the
+    pieces then skip their per-call overflow read (a host sync each); the flags are read once at the end, combined
+    over the ranks, and on an overflow every rank renders and sends again with the checks on.
+    Returns [num_frames, H, W, 3] on ``dst``, None elsewhere."""
+    if defer is not None:
+        with defer() as chk:
+            res = render_and_gather(render, tokens, cams, params, num_frames, chunks, dst, group, out, None)
+        flag = torch.tensor([1.0 if chk.overflowed() else 0.0], device=tokens.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=group)
+        if flag.item() > 0:
+            res = render_and_gather(render, tokens, cams, params, num_frames, 1, dst, group, res if res is not None else out, None)
+        return res
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    sizes = shard_sizes(num_frames, world)
+    if tokens.shape[1] != sizes[rank]:
+        raise ValueError(f"rank {rank} holds {tokens.shape[1]} frames, its shard has {sizes[rank]}")
+    cuts = [chunk_bounds(sz, chunks) for sz in sizes]
+    starts = [frame_shard(num_frames, r, world)[0] for r in range(world)]
+    reqs, keep = [], []
+    for k in range(max(1, int(chunks))):
+        a, b = cuts[rank][k], cuts[rank][k + 1]
+        img = None
+        if b > a:
+            with torch.no_grad():
+                img = render(tokens[:, a:b], {n: v[:, a:b] for n, v in cams.items()}, None,
+                             {n: v[:, a:b] for n, v in params.items()})[0][0]
+        if rank == dst:
+            if out is None:
+                if img is None:                                  # rank dst holds no frame at all: nobody does
+                    break
+                out = torch.empty((num_frames,) + tuple(img.shape[1:]), dtype=img.dtype, device=img.device)
+            if img is not None:
+                out[starts[rank] + a:starts[rank] + b].copy_(img)
+            ops = [dist.P2POp(dist.irecv, out[starts[r] + cuts[r][k]:starts[r] + cuts[r][k + 1]], r, group)
+                   for r in range(world) if r != dst and cuts[r][k + 1] > cuts[r][k]]
+            if ops:
+                reqs += dist.batch_isend_irecv(ops)              # one grouped call: all peers' pieces move concurrently
+        elif img is not None:
+            img = img.contiguous()
+            keep.append(img)                                     # alive until the send has completed
+            reqs.append(dist.isend(img, dst, group=group))
+    for q in reqs:
+        q.wait()
+    return out if rank == dst else None
+
+
+class PeerFrameGather:
+    """Gather by construction: the destination rank's frame buffer is symmetric memory mapped into every rank of
+    the box, and each rank's blend kernel stores its pixels straight into its slice of that buffer over
+    NVLink / NVSwitch (plain global stores to a peer address).  There is no separate gather step, no second copy of
+    the frames and no staging buffer: the transfer is spread over the 12 ms the blend kernel runs (1.5 GB per rank
+    = 130 GB/s per sender at 120 frames of 1024^2) instead of following it.  One device-side barrier at the end
+    tells the destination that every rank's stores have landed.
+
+    Needs the NCCL backend and peer access between the GPUs (one NVSwitch box); ``available()`` says whether the
+    symmetric-memory allocator is usable, and ``render_and_gather`` is the NCCL send/recv alternative."""
+
+    def __init__(self, num_frames: int, height: int, width: int, device, dst: int = 0, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank, self.dst = dist.get_world_size(group), dist.get_rank(group), dst
+        self.num_frames = num_frames
+        self.shape = (num_frames, height, width, 3)
+        self.local = symm.empty(self.shape, dtype=torch.float32, device=device)       # same size on every rank
+        self.handle = symm.rendezvous(self.local, self.group)
+        self.target = self.handle.get_buffer(dst, self.shape, torch.float32)          # dst's buffer, as seen from here
+        self.start, self.stop = frame_shard(num_frames, self.rank, self.world)
+
+    @staticmethod
+    def available() -> bool:
+        try:
+            import torch.distributed._symmetric_memory as symm  # noqa: F401
+            return dist.is_initialized() and dist.get_backend() == "nccl" and torch.cuda.is_available()
+        except Exception:
+            return False
+
+    def render(self, render, tokens: torch.Tensor, cams: dict, params: dict) -> Optional[torch.Tensor]:
+        """``render`` = ``Renderer.forward``; inputs are this rank's shard ([1, f_r, ...]).  Returns the whole
+        sequence [num_frames, H, W, 3] on ``dst`` (valid once the current stream has passed the barrier), None
+        elsewhere."""
+        if tokens.shape[1] != self.stop - self.start:
+            raise ValueError(f"rank {self.rank} holds {tokens.shape[1]} frames, its shard has {self.stop - self.start}")
+        if self.stop > self.start:
+            with torch.no_grad():
+                render(tokens, cams, None, params, out=self.target[self.start:self.stop])
+        self.handle.barrier()                      # every rank's kernels (and their peer stores) are complete
+        return self.local if self.rank == self.dst else None
+
+
 def shard_inputs(tokens: torch.Tensor, cams: dict, params: dict, rank: int, world: int):
     """Slice [B=1, T, ...] sequence inputs to this rank's frames."""
     T = tokens.shape[1]

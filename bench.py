@@ -50,6 +50,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gather", action="store_true")
+    ap.add_argument("--gather-chunks", type=int, default=0,
+                    help="N > 1, --gather nccl: pieces the shard is rendered and gathered in (0: 1 for N <= 2, else 4)")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: blend kernels store into rank 0's buffer over NVLink (symmetric memory), or NCCL send/recv")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "train"],
                     help="sequence = BASELINE.json configs[1] (the headline metric); train = configs[3], a secondary line")
     ap.add_argument("--loss", default="l1_ssim", choices=["l1_ssim", "l1_torch"],
@@ -258,16 +262,31 @@ def run_ours(args):
     tokens, params, cams = synthetic_inputs(Fr, size, dev, seed=rank)        # each rank: its own shard of the sequence
     params_d = {k: v.to(dev) for k, v in params.items()}
     cams_d = {k: v.to(dev) for k, v in cams.items()}
-    from audio_motion_avatar_b200.shard import gather_frames
-    gather_buf = None
-    if world > 1 and not args.no_gather and rank == 0:
-        gather_buf = torch.empty(world * Fr, size, size, 3, device=dev)
+    from audio_motion_avatar_b200.shard import PeerFrameGather, render_and_gather
+    from audio_motion_avatar_b200.renderer import deferred_overflow_checks
+    gather_buf, peer, gather_mode = None, None, "none"
+    chunks = args.gather_chunks if args.gather_chunks > 0 else (1 if world <= 2 else 4)
+    if world > 1 and not args.no_gather:
+        gather_mode = "nccl"
+        if args.gather == "peer" and PeerFrameGather.available():
+            try:
+                peer = PeerFrameGather(world * Fr, size, size, dev, dst=0)
+                gather_mode = "peer"
+            except Exception as exc:                 # no peer access / allocator unavailable: NCCL send/recv instead
+                print(f"[bench] symmetric memory unavailable ({type(exc).__name__}: {exc}); using the NCCL gather", file=sys.stderr)
+        if peer is None and rank == 0:
+            gather_buf = torch.empty(world * Fr, size, size, 3, device=dev)
 
     def step():
+        if peer is not None:
+            # frame gather (north_star) fused into the blend kernel: pixels are stored into rank 0's buffer over NVLink
+            return peer.render(r, tokens, cams_d, params_d)
+        if world > 1 and not args.no_gather:
+            # NCCL frame gather, overlapped with the render piece by piece
+            return render_and_gather(r, tokens, cams_d, params_d, world * Fr, chunks=chunks, dst=0, out=gather_buf,
+                                     defer=deferred_overflow_checks)
         with torch.no_grad():
             img, _ = r(tokens, cams_d, None, params_d)
-        if world > 1 and not args.no_gather:
-            gather_frames(img[0], world * Fr, dst=0, out=gather_buf)         # frame gather over NVLink (north_star)
         return img
 
     def barrier():
@@ -324,7 +343,8 @@ def run_ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(args), "frames_per_rank": Fr, "frames_total": world * Fr,
-                       "parallelism": f"frame-sharded x{world}" + ("" if world == 1 or args.no_gather else " + NCCL frame gather to rank 0"),
+                       "parallelism": f"frame-sharded x{world}" + {"none": "", "peer": " + frame gather to rank 0 by peer stores from the blend kernel (symmetric memory over NVLink)",
+                                                                           "nccl": f" + NCCL frame gather to rank 0 overlapped with the render ({chunks} pieces)"}[gather_mode],
                        "l2": "inputs (3 GB of triplanes per step) exceed the 126 MB L2; no flush needed"},
             "clocks": clocks.summary(), "gpu_launches": int(launches), "roofline": roofline}
 

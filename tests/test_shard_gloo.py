@@ -39,11 +39,23 @@ def _worker(rank, world, port, F, q):
         # "render": frame f -> an image filled with f
         local = torch.stack([torch.full((4, 5, 3), float(f)) for f in range(s, e)]) if e > s else torch.empty(0, 4, 5, 3)
         out = gather_frames(local, F, dst=0)
+        # the pipelined variant: "render" pieces of the shard and gather them as they come (3 pieces, ragged)
+        from audio_motion_avatar_b200.shard import render_and_gather
+        calls = []
+
+        def fake_render(tok, cm2, _none, pr2):
+            calls.append(tok.shape[1])
+            frames = pr2["transl"][0, :, 0] / 3.0                       # transl[f] = (3f, 3f+1, 3f+2) -> frame index
+            return torch.stack([torch.full((4, 5, 3), float(v)) for v in frames])[None], None
+
+        out2 = render_and_gather(fake_render, tk, cm, pr, F, chunks=3, dst=0)
         if rank == 0:
             ok = out is not None and out.shape == (F, 4, 5, 3) and all(torch.all(out[f] == f) for f in range(F))
+            ok = ok and out2 is not None and out2.shape == (F, 4, 5, 3) and all(torch.all(out2[f] == f) for f in range(F))
             q.put(bool(ok))
         else:
-            assert out is None
+            assert out is None and out2 is None
+        assert sum(calls) == e - s
         dist.barrier()
     finally:
         dist.destroy_process_group()
