@@ -371,7 +371,8 @@ def run_ours(args):
                        "d2h_bytes_per_step": out_h.numel() * 4, "ms_per_step": sec / steps * 1e3,
                        "api": f"Renderer.render_sequence(chunk={args.chunk}), pinned host buffers, 3 streams"}
         # the pipelined host path must produce the frames of the device-resident path
-        img = step()
+        with torch.no_grad():
+            img, _ = r(tokens, cams_d, None, params_d)               # this rank's shard, device-resident path
         torch.cuda.synchronize()
         line["e2e"]["max_abs_vs_device_path"] = float((out_h.to(dev) - img).abs().max().item())
         del tok_h, out_h
