@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(BLEND_THREADS, 5) blend_kernel(const BlendPara
     // per warp: shared addresses (record base + 48 j) of the batch entries that touch its rectangle
     __shared__ __align__(4) unsigned short s_list[BLEND_THREADS / 32][BLEND_THREADS];
     __shared__ unsigned int s_next;
-    __shared__ __align__(16) float s_out[ROWS ? 16 * 48 : 4];       // one tile of HWC colour
+    __shared__ __align__(16) float s_out[ROWS ? 16 * 96 : 4];       // ROWS: HWC colour of a pair of tiles
     const int tiles = p.gx * p.gy;
     const unsigned int total_tiles = (unsigned int)((int64_t)p.F * tiles);
     const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
@@ -63,12 +63,23 @@ __global__ void __launch_bounds__(BLEND_THREADS, 5) blend_kernel(const BlendPara
         // tile from a device counter instead of striding, so no SM idles behind a column of deep tiles
         if (threadIdx.x == 0) s_next = atomicAdd(p.work_counter, 1u);
         __syncthreads();
-        unsigned int t;
-        if (!queue_tile(s_next, p.order, p.tile_start, total_tiles, t)) break;
-        if (t == 0xffffffffu) { __syncthreads(); continue; }       // deep tile, already handed out
-        const int f = (int)(t / tiles);
-        const int tile = (int)(t - (unsigned int)f * tiles);
-        const int ty = tile / p.gx, tx = tile - ty * p.gx;
+        // ROWS: the work unit is a PAIR of horizontally adjacent tiles (W is a multiple of 32), so that the colour leaves
+        // as rows of 384 contiguous bytes = three full 128-byte lines; plain frame order (these are long launches)
+        unsigned int t0;
+        if (ROWS) {
+            if (s_next >= total_tiles / 2) break;
+            t0 = 2u * s_next;
+        } else {
+            if (!queue_tile(s_next, p.order, p.tile_start, total_tiles, t0)) break;
+            if (t0 == 0xffffffffu) { __syncthreads(); continue; }  // deep tile, already handed out
+        }
+        const int f = (int)(t0 / tiles);
+        const int tile0 = (int)(t0 - (unsigned int)f * tiles);
+        const int ty = tile0 / p.gx;
+#pragma unroll 1
+        for (int half = 0; half < (ROWS ? 2 : 1); ++half) {
+        const unsigned int t = t0 + half;
+        const int tx = tile0 - ty * p.gx + half;
         const int pxi = tx * 16 + lx, pyi = ty * 16 + ly;
         const bool inside = pxi < p.W && pyi < p.H;
         float pxf, pyf;                             // pinned: ptxas otherwise re-converts them inside the list walk
@@ -169,7 +180,6 @@ __global__ void __launch_bounds__(BLEND_THREADS, 5) blend_kernel(const BlendPara
         // colour: HWC tiles that lie inside the image horizontally go through shared memory and leave as 16 rows of
         // 192 contiguous bytes (12 float4 stores per row) instead of 256 x 3 scalar stores; what matters is the
         // multi-GPU gather, where `out_color` is another GPU's memory and NVLink moves full segments, not 12-byte pixels
-        const bool row_stores = ROWS && tx * 16 + 16 <= p.W;                         // uniform across the CTA
         const int64_t hw = (int64_t)p.H * p.W;
         float o0 = 0.0f, o1 = 0.0f, o2 = 0.0f;
         if (inside) {
@@ -181,7 +191,7 @@ __global__ void __launch_bounds__(BLEND_THREADS, 5) blend_kernel(const BlendPara
                 o2 = fminf(fmaxf(o2, 0.0f), 1.0f);
             }
             const int64_t pix = (int64_t)pyi * p.W + pxi;
-            if (!row_stores) {
+            if (!ROWS) {
                 if (p.hwc) {
                     float *o = p.out_color + ((int64_t)f * hw + pix) * 3;
                     o[0] = o0; o[1] = o1; o[2] = o2;
@@ -194,26 +204,25 @@ __global__ void __launch_bounds__(BLEND_THREADS, 5) blend_kernel(const BlendPara
             if (p.n_contrib) p.n_contrib[(int64_t)f * hw + pix] = last;
             if (DEPTH) p.out_invdepth[(int64_t)f * hw + pix] = Dv;
         }
-        if (row_stores) {
-            const int row = threadIdx.x / 12, q = threadIdx.x - row * 12;             // threads 0..191: one float4 each
-            float4 v;
-            if (r1 > r0) {                           // uniform: four tiles in five are empty and skip the staging
-                float *so = s_out + ly * 48 + lx * 3;
-                so[0] = o0; so[1] = o1; so[2] = o2;
-                __syncthreads();
-                if (threadIdx.x < 192) v = reinterpret_cast<const float4 *>(s_out + row * 48)[q];
-            } else {                                 // background only: (b0 b1 b2 b0)(b1 b2 b0 b1)(b2 b0 b1 b2)...
-                float c0 = bg0, c1 = bg1, c2 = bg2;
-                if (p.clamp01) {
-                    c0 = fminf(fmaxf(c0, 0.0f), 1.0f); c1 = fminf(fmaxf(c1, 0.0f), 1.0f); c2 = fminf(fmaxf(c2, 0.0f), 1.0f);
-                }
-                const int ph = q % 3;
-                v = ph == 0 ? make_float4(c0, c1, c2, c0) : ph == 1 ? make_float4(c1, c2, c0, c1) : make_float4(c2, c0, c1, c2);
-            }
-            if (threadIdx.x < 192 && ty * 16 + row < p.H)
-                reinterpret_cast<float4 *>(p.out_color + ((int64_t)f * hw + (int64_t)(ty * 16 + row) * p.W + tx * 16) * 3)[q] = v;
+        if (ROWS) {                                  // stage this tile's colour: row ly, 96 floats per row of the pair
+            float *so = s_out + ly * 96 + half * 48 + lx * 3;
+            so[0] = o0; so[1] = o1; so[2] = o2;
         }
         __syncthreads();
+        }                                            // half
+        if (ROWS) {
+            // HWC colour of the tile pair: 16 rows x 384 contiguous bytes (24 float4 per row).  What matters is the
+            // multi-GPU gather, where `out_color` is another GPU's memory: NVLink moves full lines, not 12-byte pixels
+            const int64_t hw = (int64_t)p.H * p.W;
+            const int tx0 = tile0 - ty * p.gx;
+            for (int i = threadIdx.x; i < 16 * 24; i += BLEND_THREADS) {
+                const int row = i / 24, q = i - row * 24;
+                if (ty * 16 + row < p.H)
+                    reinterpret_cast<float4 *>(p.out_color + ((int64_t)f * hw + (int64_t)(ty * 16 + row) * p.W + tx0 * 16) * 3)[q] =
+                        reinterpret_cast<const float4 *>(s_out + row * 96)[q];
+            }
+            __syncthreads();                         // s_out is free for the next pair
+        }
     }
 }
 
@@ -231,11 +240,11 @@ extern "C" int amav_splat_blend(const AmavSplatDims *d, const float *geom, const
     BlendParams p;
     p.F = d->frames; p.N = d->num_gaussians; p.W = d->width; p.H = d->height;
     p.gx = (d->width + 15) / 16; p.gy = (d->height + 15) / 16; p.hwc = hwc; p.clamp01 = clamp01;
-    // Row stores (a tile's colour leaves as 16 x 192 contiguous bytes) when the output buffer lives on ANOTHER GPU
-    // (shard.PeerFrameGather: NVLink moves segments, not 12-byte pixels; 8 GPUs: 34.7k -> 43.0k frames/s).  For local
-    // memory the plain per-pixel stores are kept: the extra code costs the list walk ~4% through register allocation.
+    // Row stores (the colour of a pair of tiles leaves as 16 x 384 contiguous bytes) when the output buffer lives on
+    // ANOTHER GPU (shard.PeerFrameGather: NVLink moves lines, not 12-byte pixels).  For local memory the plain
+    // per-pixel stores are kept: the extra code costs the list walk ~4% through register allocation.
     int rows = 0;
-    if (hwc && d->width % 4 == 0 && ((uintptr_t)out_color & 15) == 0) {          // every tile row is 16-byte aligned
+    if (hwc && d->width % 32 == 0 && ((uintptr_t)out_color & 15) == 0 && !final_T && !n_contrib) {    // inference, whole tile pairs
         cudaPointerAttributes attr;
         int dev = -1;
         if (cudaGetDevice(&dev) == cudaSuccess && cudaPointerGetAttributes(&attr, out_color) == cudaSuccess)
