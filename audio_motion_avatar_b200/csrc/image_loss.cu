@@ -37,72 +37,111 @@ __device__ __forceinline__ float block_sum_256(float v, float *s_part)
     return t;                          // valid on thread 0
 }
 
+// Separable 11-tap filter with register sliding windows: one work item produces LG consecutive outputs along the
+// filter direction from LG + 10 inputs held in registers, so an output costs (LG + 10) / LG shared-memory loads per
+// filtered quantity instead of 11 (the kernels were bound by the LDS pipe, not by FMAs).  All three channels of a tile
+// go through one pass: 26 x 26 x 3 halo of both images -> horizontal pass (26 rows x 16 columns x 3 channels, five
+// moments) -> vertical pass -> SSIM.
+constexpr int LG = 4;                  // outputs per work item along the filter direction
+constexpr int LCH = 3;                 // channels
+
 __global__ void __launch_bounds__(256) image_loss_fwd_kernel(int H, int W, const float *__restrict__ img,
                                                               const float *__restrict__ gt, const Window win,
                                                               float *__restrict__ sums, float *__restrict__ maps)
 {
-    __shared__ float s_x[LH][LH + 1], s_y[LH][LH + 1];
-    __shared__ float s_h[5][LH][LT + 1];
+    __shared__ float s_x[LCH][LH][LH + 1], s_y[LCH][LH][LH + 1];
+    __shared__ float s_h[LCH][5][LH][LT + 4];          // row stride 20: the vertical pass's two row groups per warp hit disjoint banks
     __shared__ float s_part[8];
     const int f = blockIdx.z;
     const int tx0 = blockIdx.x * LT, ty0 = blockIdx.y * LT;
-    const int lx = threadIdx.x & (LT - 1), ly = threadIdx.x >> 4;
-    const int px = tx0 + lx, py = ty0 + ly;
-    const bool inside = px < W && py < H;
     const int64_t hw = (int64_t)H * W;
     const float *xf = img + (int64_t)f * hw * 3, *yf = gt + (int64_t)f * hw * 3;
+    // halo of both images, all channels (HWC: a pixel's three floats are contiguous)
+    for (int i = threadIdx.x; i < LH * LH * LCH; i += 256) {
+        const int pix = i / LCH, c = i - pix * LCH;
+        const int r = pix / LH, q = pix - r * LH;
+        const int gy = ty0 + r - LR, gx = tx0 + q - LR;
+        float a = 0.0f, b = 0.0f;
+        if (gx >= 0 && gx < W && gy >= 0 && gy < H) {
+            a = xf[((int64_t)gy * W + gx) * 3 + c];
+            b = yf[((int64_t)gy * W + gx) * 3 + c];
+        }
+        s_x[c][r][q] = a; s_y[c][r][q] = b;
+    }
+    __syncthreads();
+    // horizontal pass: item = (channel, row, group of LG columns)
+    for (int i = threadIdx.x; i < LCH * LH * (LT / LG); i += 256) {
+        const int g = i % (LT / LG), r = (i / (LT / LG)) % LH, c = i / ((LT / LG) * LH);
+        float a[LG + 2 * LR], b[LG + 2 * LR];
+#pragma unroll
+        for (int k = 0; k < LG + 2 * LR; ++k) { a[k] = s_x[c][r][g * LG + k]; b[k] = s_y[c][r][g * LG + k]; }
+        float m[5][LG];
+#pragma unroll
+        for (int o = 0; o < LG; ++o) { m[0][o] = m[1][o] = m[2][o] = m[3][o] = m[4][o] = 0.0f; }
+#pragma unroll
+        for (int k = 0; k < LG + 2 * LR; ++k) {
+            const float aa = a[k] * a[k], bb = b[k] * b[k], ab = a[k] * b[k];
+#pragma unroll
+            for (int o = 0; o < LG; ++o) {
+                const int t = k - o;                           // tap index of input k for output o
+                if (t >= 0 && t <= 2 * LR) {
+                    const float w = win.w[t];
+                    m[0][o] = fmaf(w, a[k], m[0][o]); m[1][o] = fmaf(w, b[k], m[1][o]);
+                    m[2][o] = fmaf(w, aa, m[2][o]); m[3][o] = fmaf(w, bb, m[3][o]); m[4][o] = fmaf(w, ab, m[4][o]);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+#pragma unroll
+            for (int o = 0; o < LG; ++o) s_h[c][q][r][g * LG + o] = m[q][o];
+    }
+    __syncthreads();
+    // vertical pass + SSIM: item = (channel, group of LG rows, column); consecutive threads = consecutive columns
     float l1 = 0.0f, ss = 0.0f;
-    for (int c = 0; c < 3; ++c) {
-        __syncthreads();
-        for (int i = threadIdx.x; i < LH * LH; i += 256) {
-            const int r = i / LH, q = i - r * LH;
-            const int gy = ty0 + r - LR, gx = tx0 + q - LR;
-            float a = 0.0f, b = 0.0f;
-            if (gx >= 0 && gx < W && gy >= 0 && gy < H) {
-                a = xf[((int64_t)gy * W + gx) * 3 + c];
-                b = yf[((int64_t)gy * W + gx) * 3 + c];
-            }
-            s_x[r][q] = a; s_y[r][q] = b;
-        }
-        __syncthreads();
-        // horizontal pass: LH rows x LT columns, five moments
-        for (int i = threadIdx.x; i < LH * LT; i += 256) {
-            const int r = i >> 4, q = i & (LT - 1);
-            float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f, m4 = 0.f;
+    for (int i = threadIdx.x; i < LCH * (LT / LG) * LT; i += 256) {
+        const int lx = i % LT, g = (i / LT) % (LT / LG), c = i / (LT * (LT / LG));
+        float v[5][LG];
 #pragma unroll
-            for (int k = 0; k <= 2 * LR; ++k) {
-                const float a = s_x[r][q + k], b = s_y[r][q + k], w = win.w[k];
-                m0 = fmaf(w, a, m0); m1 = fmaf(w, b, m1);
-                m2 = fmaf(w, a * a, m2); m3 = fmaf(w, b * b, m3); m4 = fmaf(w, a * b, m4);
-            }
-            s_h[0][r][q] = m0; s_h[1][r][q] = m1; s_h[2][r][q] = m2; s_h[3][r][q] = m3; s_h[4][r][q] = m4;
-        }
-        __syncthreads();
-        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+        for (int o = 0; o < LG; ++o) { v[0][o] = v[1][o] = v[2][o] = v[3][o] = v[4][o] = 0.0f; }
 #pragma unroll
-        for (int k = 0; k <= 2 * LR; ++k) {
-            const float w = win.w[k];
-            mu1 = fmaf(w, s_h[0][ly + k][lx], mu1); mu2 = fmaf(w, s_h[1][ly + k][lx], mu2);
-            e11 = fmaf(w, s_h[2][ly + k][lx], e11); e22 = fmaf(w, s_h[3][ly + k][lx], e22);
-            e12 = fmaf(w, s_h[4][ly + k][lx], e12);
+        for (int k = 0; k < LG + 2 * LR; ++k) {
+            float h[5];
+#pragma unroll
+            for (int q = 0; q < 5; ++q) h[q] = s_h[c][q][g * LG + k][lx];
+#pragma unroll
+            for (int o = 0; o < LG; ++o) {
+                const int t = k - o;
+                if (t >= 0 && t <= 2 * LR) {
+                    const float w = win.w[t];
+#pragma unroll
+                    for (int q = 0; q < 5; ++q) v[q][o] = fmaf(w, h[q], v[q][o]);
+                }
+            }
         }
-        if (inside) {
-            const float x = s_x[ly + LR][lx + LR], y = s_y[ly + LR][lx + LR];
-            l1 += fabsf(x - y);
-            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-            const float sig1 = e11 - mu1_sq, sig2 = e22 - mu2_sq, sig12 = e12 - mu12;
-            const float A1 = 2.0f * mu12 + SSIM_C1, A2 = 2.0f * sig12 + SSIM_C2;
-            const float B1 = mu1_sq + mu2_sq + SSIM_C1, B2 = sig1 + sig2 + SSIM_C2;
-            const float inv = 1.0f / (B1 * B2);
-            const float S = A1 * A2 * inv;
-            ss += S;
-            if (maps) {
-                // S as a function of (mu1, E[x^2], E[xy]) with sigma1^2 = E[x^2] - mu1^2, sigma12 = E[xy] - mu1 mu2
-                const float dS_de11 = -S / B2;
-                const float dS_de12 = 2.0f * A1 * inv;
-                const float dS_dmu1 = 2.0f * mu2 * (A2 - A1) * inv - S * 2.0f * mu1 * (B2 - B1) * inv;
-                float *m = maps + ((int64_t)f * 3 + c) * 3 * hw + (int64_t)py * W + px;
-                m[0] = dS_dmu1; m[hw] = dS_de11; m[2 * hw] = dS_de12;
+        const int px = tx0 + lx;
+#pragma unroll
+        for (int o = 0; o < LG; ++o) {
+            const int ly = g * LG + o, py = ty0 + ly;
+            if (px < W && py < H) {
+                const float mu1 = v[0][o], mu2 = v[1][o], e11 = v[2][o], e22 = v[3][o], e12 = v[4][o];
+                const float x = s_x[c][ly + LR][lx + LR], y = s_y[c][ly + LR][lx + LR];
+                l1 += fabsf(x - y);
+                const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+                const float sig1 = e11 - mu1_sq, sig2 = e22 - mu2_sq, sig12 = e12 - mu12;
+                const float A1 = 2.0f * mu12 + SSIM_C1, A2 = 2.0f * sig12 + SSIM_C2;
+                const float B1 = mu1_sq + mu2_sq + SSIM_C1, B2 = sig1 + sig2 + SSIM_C2;
+                const float inv = 1.0f / (B1 * B2);
+                const float S = A1 * A2 * inv;
+                ss += S;
+                if (maps) {
+                    // S as a function of (mu1, E[x^2], E[xy]) with sigma1^2 = E[x^2] - mu1^2, sigma12 = E[xy] - mu1 mu2
+                    const float dS_de11 = -S / B2;
+                    const float dS_de12 = 2.0f * A1 * inv;
+                    const float dS_dmu1 = 2.0f * mu2 * (A2 - A1) * inv - S * 2.0f * mu1 * (B2 - B1) * inv;
+                    float *mp = maps + ((int64_t)f * 3 + c) * 3 * hw + (int64_t)py * W + px;
+                    mp[0] = dS_dmu1; mp[hw] = dS_de11; mp[2 * hw] = dS_de12;
+                }
             }
         }
     }
@@ -111,6 +150,8 @@ __global__ void __launch_bounds__(256) image_loss_fwd_kernel(int H, int W, const
     if (threadIdx.x == 0) { atomicAdd(sums + 2 * f, t1); atomicAdd(sums + 2 * f + 1, t2); }
 }
 
+// (One channel at a time and one tap per shared-memory load here: with the 41 KB the three-channel sliding-window
+// variant needs, this kernel fell from 8 to 4 CTAs per SM and got slower, 0.34 -> 0.41 ms.)
 // dL/dx = g_l1[f] * sign(x - y) + g_ssim[f] * (conv(dS/dmu1) + 2 x conv(dS/dE[x^2]) + y conv(dS/dE[xy]))
 __global__ void __launch_bounds__(256) image_loss_bwd_kernel(int H, int W, const float *__restrict__ img,
                                                               const float *__restrict__ gt, const Window win,
