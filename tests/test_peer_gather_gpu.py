@@ -22,7 +22,7 @@ def _worker(rank, world, port, q):
         from audio_motion_avatar_b200 import synthetic as S
         from audio_motion_avatar_b200.renderer import Renderer
         from audio_motion_avatar_b200.shard import PeerFrameGather, frame_shard, render_and_gather, shard_inputs
-        H, W, C, R, T = 64, 48, 64, 16, 5                              # 5 frames over 2 ranks: ragged 3 + 2
+        H, W, C, R, T = 72, 64, 64, 16, 5                              # 5 frames over 2 ranks: ragged 3 + 2; W % 32 == 0: row stores
         cfg = SimpleNamespace(device=f"cuda:{rank}", triplane_resolution=R, triplane_feature_dim=C, radius=1.4,
                               smplx_model_path=None, flat_hand_mean=True, num_expression_coeffs=10, upsample_triplane=False,
                               densify_smplx_verts=False, subdivide_steps=2, predict_smplx_params=False, no_point_refiner=True,
