@@ -140,7 +140,10 @@ __global__ void __launch_bounds__(PBB_THREADS) pose_blend_bwd_kernel(int F, int 
     const int slot = butterfly16_slot(lane);
     const float *pd = posedirs + (int64_t)3 * (live ? v : 0);
     const int64_t ld = (int64_t)3 * V;
-    for (int k = 0; k < K; ++k) {
+    // blockIdx.z splits the K pose-feature rows (few frames = few CTAs otherwise: 82 for a 4-subject training step)
+    const int kchunk = (K + (int)gridDim.z - 1) / (int)gridDim.z;
+    const int k_begin = (int)blockIdx.z * kchunk, k_end = min(K, k_begin + kchunk);
+    for (int k = k_begin; k < k_end; ++k) {
         const float p0 = live ? __ldg(pd + k * ld) : 0.0f, p1 = live ? __ldg(pd + k * ld + 1) : 0.0f,
                     p2 = live ? __ldg(pd + k * ld + 2) : 0.0f;
         float a[16];
@@ -149,7 +152,7 @@ __global__ void __launch_bounds__(PBB_THREADS) pose_blend_bwd_kernel(int F, int 
         const float r = butterfly16(a, lane);
         if ((lane & 1) == 0) atomicAdd(&s_out[k * PBB_F + slot], r);
     }
-    for (int s = 0; s < S; ++s) {
+    for (int s = 0; s < (blockIdx.z == 0 ? S : 0); ++s) {
         const float *sd = shapedirs + (int64_t)(live ? v : 0) * 3 * S + s;
         const float p0 = live ? __ldg(sd) : 0.0f, p1 = live ? __ldg(sd + S) : 0.0f, p2 = live ? __ldg(sd + 2 * S) : 0.0f;
         float a[16];
@@ -333,6 +336,8 @@ extern "C" int amav_lbs_backward(int F, int V, int J, int S, const float *full_p
     AMAV_CHECK_ARG(smem <= 200 * 1024, "pose basis too large");
     cudaFuncSetAttribute(pose_blend_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 gb(amav_div_up(V, PBB_THREADS), amav_div_up(F, PBB_F));
+    const int ksplit = (4 * AMAV_SM_COUNT + (int)(gb.x * gb.y) - 1) / (int)(gb.x * gb.y);
+    gb.z = ksplit < 1 ? 1 : (ksplit > 8 ? 8 : ksplit);
     pose_blend_bwd_kernel<<<gb, PBB_THREADS, smem, stream>>>(F, V, S, K, d_v_posed, shapedirs, posedirs, d_pose_feature, d_shape);
     chain_bwd_kernel<<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, d_A, d_pose_feature,
                                            d_full_pose, d_shape);
