@@ -271,9 +271,14 @@ def run_ours(args):
         if args.gather == "peer" and PeerFrameGather.available():
             try:
                 peer = PeerFrameGather(world * Fr, size, size, dev, dst=0)
-                gather_mode = "peer"
             except Exception as exc:                 # no peer access / allocator unavailable: NCCL send/recv instead
                 print(f"[bench] symmetric memory unavailable ({type(exc).__name__}: {exc}); using the NCCL gather", file=sys.stderr)
+            ok = torch.tensor([1.0 if peer is not None else 0.0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)            # every rank takes the same path
+            if ok.item() > 0:
+                gather_mode = "peer"
+            else:
+                peer = None
         if peer is None and rank == 0:
             gather_buf = torch.empty(world * Fr, size, size, 3, device=dev)
 
