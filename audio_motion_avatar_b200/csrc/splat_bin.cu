@@ -231,8 +231,10 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB,
     // pass 1: bin of every entry (kept in registers) + bin counts
     uint64_t ent[PER];
     int bin[PER];
+    const int slots = (n + T - 1) / T;                    // slots in use (uniform): the unrolled loops stop there
 #pragma unroll
     for (int k = 0; k < PER; ++k) {
+        if (k >= slots) break;
         const int i = threadIdx.x + k * T;
         if (i < n) {
             ent[k] = s_ent[i];
@@ -263,6 +265,7 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB,
     // pass 2: scatter (slot inside the bin from an atomic cursor: any order, the bin is sorted next)
 #pragma unroll
     for (int k = 0; k < PER; ++k) {
+        if (k >= slots) break;
         const int i = threadIdx.x + k * T;
         if (i < n) s_ent[atomicAdd(&s_bin[bin[k]], 1u)] = ent[k];
     }
@@ -271,6 +274,7 @@ __device__ bool bin_sort_tile(uint64_t *s_ent, uint32_t *s_bin, int n, int logB,
     // the (about one, at most SORT_MAX_BIN) entries of its bin, and its Gaussian index goes straight to the output.
 #pragma unroll
     for (int k = 0; k < PER; ++k) {
+        if (k >= slots) break;
         const int i = threadIdx.x + k * T;
         if (i < n) {
             const int e0 = bin[k] == 0 ? 0 : (int)s_bin[bin[k] - 1], e1 = (int)s_bin[bin[k]];
@@ -298,6 +302,8 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
     uint32_t *s_bin = reinterpret_cast<uint32_t *>(s_sort + CAP);        // [CAP]
     __shared__ unsigned int s_next;
     __shared__ uint32_t s_ts[POP + 1];
+    __shared__ unsigned int s_mask[2];
+    static_assert(POP <= 64, "one mask word per 32 popped tiles");
     const int tid = threadIdx.x;
     for (;;) {
         __syncthreads();
@@ -308,22 +314,32 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
         const unsigned int nt = min((unsigned int)POP, num_tiles_total - t0);
         if (tid <= (int)nt) s_ts[tid] = tile_start[t0 + tid];
         __syncthreads();
-        if (MINN > 0) {                                            // large-bucket instantiation: most batches hold none
-            const bool mine = tid < (int)nt && (int64_t)s_ts[tid + 1] - (int64_t)s_ts[tid] > MINN;
-            if (!__syncthreads_or(mine)) continue;
+        // which of the popped tiles this instantiation sorts (four in five are empty; the large-bucket instantiation
+        // finds none in most batches): one lane per tile, then the CTA walks the set bits only
+        if (tid < 64) {
+            bool mine = false;
+            if (tid < (int)nt) {
+                int64_t e = s_ts[tid + 1];
+                if (e > capacity) e = capacity;
+                const int64_t n = e - (int64_t)s_ts[tid];
+                mine = n > MINN && n >= 1 && (GLOBAL_FALLBACK || n <= CAP);
+            }
+            const unsigned int m = __ballot_sync(0xffffffffu, mine);
+            if ((tid & 31) == 0) s_mask[tid >> 5] = m;
         }
-        for (unsigned int q = 0; q < nt; ++q) {
+        __syncthreads();
+        for (int w = 0; w < (POP + 31) / 32; ++w)
+        for (unsigned int todo = s_mask[w]; todo != 0u; todo &= todo - 1u) {
+            const unsigned int q = 32u * w + (unsigned int)(__ffs(todo) - 1);
             const int64_t s = s_ts[q];
             int64_t e = s_ts[q + 1];
             if (e > capacity) e = capacity;
             const int n = (int)(e - s);
-            if (n <= MINN || (!GLOBAL_FALLBACK && n > CAP)) continue;     // uniform across the CTA
             if (n == 1) {
                 if (tid == 0) point_list[s] = (int32_t)(uint32_t)entries[s];
                 continue;
             }
-            int logP = 1;
-            while ((1 << logP) < n) ++logP;
+            const int logP = max(1, 32 - __clz(n - 1));            // smallest power of two >= n
             __syncthreads();                                       // the previous tile is done with shared memory
             if (n > CAP) {
                 uint64_t *g = entries + s;
@@ -342,8 +358,7 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
                 }
                 continue;
             }
-            int logB = logP;
-            while ((1 << logB) < T) ++logB;
+            const int logB = max(logP, 31 - __clz(T));
             if (!bin_sort_tile<T, CAP / T>(s_ent, s_bin, n, logB, point_list + s)) {
                 __syncthreads();
                 bitonic_sort(s_ent, n, logP);
