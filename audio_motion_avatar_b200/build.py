@@ -25,6 +25,7 @@ SOURCES = [
     ("lbs_bwd.cu", []),
     ("image_loss.cu", []),
     ("camera.cu", ["-fmad=false"]),
+    ("video_sink.cu", []),
 ]
 COMMON = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
           "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]

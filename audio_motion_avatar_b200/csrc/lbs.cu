@@ -52,7 +52,12 @@ __global__ void __launch_bounds__(256) lbs_precompute_kernel(int V, int J, int S
 }
 
 // ---------------------------------------------------------------------------------------------
-// one CTA (64 threads) per frame
+// one CTA (64 threads) per frame.  SIXD = false: full_pose [F,J,3] axis-angles through smplx's Rodrigues;
+// SIXD = true: full_pose [F,J,6] in the 6D rotation representation the SMPL-X parameter decoder's heads emit, turned
+// into R by Gram-Schmidt (pytorch3d.transforms.rotation_6d_to_matrix: rows b1 = a1/|a1|, b2 = (a2 - (b1.a2) b1)/|.|,
+// b3 = b1 x b2) -- the reference goes 6D -> matrix -> matrix_to_axis_angle -> batch_rodrigues -> the same matrix
+// (src/models/smplx_decoder.py:106-127 then renderer.py:104-118, :261-274).
+template <bool SIXD>
 __global__ void __launch_bounds__(64) lbs_pose_kernel(int J, int S, const float *__restrict__ full_pose,
                                                       const float *__restrict__ shape_comp,
                                                       const float *__restrict__ J_template,
@@ -68,6 +73,21 @@ __global__ void __launch_bounds__(64) lbs_pose_kernel(int J, int S, const float 
     __shared__ int s_par[MAXJ];
     const int t = threadIdx.x;
     if (t < J) {
+        float R[9];
+        if (SIXD) {
+            const float *d6 = full_pose + ((int64_t)f * J + t) * 6;
+            const float a1x = d6[0], a1y = d6[1], a1z = d6[2], a2x = d6[3], a2y = d6[4], a2z = d6[5];
+            // F.normalize: v / max(||v||, 1e-12)
+            const float n1 = fmaxf(sqrtf(a1x * a1x + a1y * a1y + a1z * a1z), 1e-12f);
+            const float b1x = a1x / n1, b1y = a1y / n1, b1z = a1z / n1;
+            const float dt = b1x * a2x + b1y * a2y + b1z * a2z;
+            const float ux = a2x - dt * b1x, uy = a2y - dt * b1y, uz = a2z - dt * b1z;
+            const float n2 = fmaxf(sqrtf(ux * ux + uy * uy + uz * uz), 1e-12f);
+            const float b2x = ux / n2, b2y = uy / n2, b2z = uz / n2;
+            R[0] = b1x; R[1] = b1y; R[2] = b1z;
+            R[3] = b2x; R[4] = b2y; R[5] = b2z;
+            R[6] = b1y * b2z - b1z * b2y; R[7] = b1z * b2x - b1x * b2z; R[8] = b1x * b2y - b1y * b2x;
+        } else {
         // smplx.lbs.batch_rodrigues: angle = ||r + 1e-8||, dir = r / angle, R = I + sin K + (1-cos) K K
         const float rx = full_pose[((int64_t)f * J + t) * 3], ry = full_pose[((int64_t)f * J + t) * 3 + 1],
                     rz = full_pose[((int64_t)f * J + t) * 3 + 2];
@@ -78,10 +98,10 @@ __global__ void __launch_bounds__(64) lbs_pose_kernel(int J, int S, const float 
         sincosf(angle, &sn, &cs);
         const float oc = 1.0f - cs;
         // K = [[0,-z,y],[z,0,-x],[-y,x,0]];  K K = [[-(y2+z2), xy, xz],[xy, -(x2+z2), yz],[xz, yz, -(x2+y2)]]
-        float R[9];
         R[0] = 1.0f + oc * (-(y * y + z * z)); R[1] = sn * (-z) + oc * (x * y);   R[2] = sn * y + oc * (x * z);
         R[3] = sn * z + oc * (x * y);          R[4] = 1.0f + oc * (-(x * x + z * z)); R[5] = sn * (-x) + oc * (y * z);
         R[6] = sn * (-y) + oc * (x * z);       R[7] = sn * x + oc * (y * z);      R[8] = 1.0f + oc * (-(x * x + y * y));
+        }
 #pragma unroll
         for (int k = 0; k < 9; ++k) s_R[t][k] = R[k];
         if (t > 0) {
@@ -276,7 +296,7 @@ extern "C" int amav_lbs_precompute(int V, int J, int S, const float *v_template,
     return AMAV_OK;
 }
 
-extern "C" int amav_lbs_forward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
+static int lbs_forward_impl(bool sixd, int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
                                 const float *v_template, const float *shapedirs, const float *posedirs,
                                 const int32_t *parents, const float *J_template, const float *J_dirs,
                                 const float *weights_T, float *pose_feature, float *joints, float *A, float *v_posed,
@@ -290,7 +310,10 @@ extern "C" int amav_lbs_forward(int F, int V, int J, int S, const float *full_po
     AMAV_CHECK_ARG(((uintptr_t)A & 15) == 0, "A must be 16-byte aligned");
     cudaStream_t stream = (cudaStream_t)stream_;
     const int K = (J - 1) * 9;
-    lbs_pose_kernel<<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, pose_feature, joints, A);
+    if (sixd)
+        lbs_pose_kernel<true><<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, pose_feature, joints, A);
+    else
+        lbs_pose_kernel<false><<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, pose_feature, joints, A);
     const size_t smem = (size_t)(K + S) * PB_F * sizeof(float);
     AMAV_CHECK_ARG(smem <= 200 * 1024, "pose basis too large");
     cudaFuncSetAttribute(pose_blend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -303,6 +326,26 @@ extern "C" int amav_lbs_forward(int F, int V, int J, int S, const float *full_po
     amav_count_launches(2);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
+}
+
+extern "C" int amav_lbs_forward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
+                                const float *v_template, const float *shapedirs, const float *posedirs,
+                                const int32_t *parents, const float *J_template, const float *J_dirs,
+                                const float *weights_T, float *pose_feature, float *joints, float *A, float *v_posed,
+                                float *verts, void *stream)
+{
+    return lbs_forward_impl(false, F, V, J, S, full_pose, shape_comp, v_template, shapedirs, posedirs, parents, J_template, J_dirs,
+                            weights_T, pose_feature, joints, A, v_posed, verts, stream);
+}
+
+extern "C" int amav_lbs_forward_6d(int F, int V, int J, int S, const float *pose_6d, const float *shape_comp,
+                                const float *v_template, const float *shapedirs, const float *posedirs,
+                                const int32_t *parents, const float *J_template, const float *J_dirs,
+                                const float *weights_T, float *pose_feature, float *joints, float *A, float *v_posed,
+                                float *verts, void *stream)
+{
+    return lbs_forward_impl(true, F, V, J, S, pose_6d, shape_comp, v_template, shapedirs, posedirs, parents, J_template, J_dirs,
+                            weights_T, pose_feature, joints, A, v_posed, verts, stream);
 }
 
 extern "C" int amav_densify_gather(int F, int V, int N, int P, const float *verts, const int32_t *par,

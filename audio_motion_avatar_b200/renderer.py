@@ -299,9 +299,19 @@ class Renderer(nn.Module):
         return self._fixed_idx
 
     def get_smpl_vertices(self, smpl_params):
-        """renderer.py:245-290: posed vertices (no transl), optionally densified + subset -> [B*T, N, 3]."""
-        full, shape = self.smplx_model.full_pose(smpl_params)
-        verts = stages.lbs_vertices(self.smplx_model, full, shape)
+        """renderer.py:245-290: posed vertices (no transl), optionally densified + subset -> [B*T, N, 3].
+
+        A dict that carries ``pose_6d`` [..., J, 6] (stages.pose_6d_from_decoder_heads: the SMPL-X parameter decoder's
+        6D heads, smplx_decoder.py:106-127) instead of the axis-angle keys goes through amav_lbs_forward_6d, without the
+        reference's matrix -> axis-angle -> Rodrigues round trip (forward only)."""
+        if "pose_6d" in smpl_params:
+            shape = torch.cat([smpl_params["betas"].reshape(-1, smpl_params["betas"].shape[-1]),
+                               smpl_params["expression"].reshape(-1, smpl_params["expression"].shape[-1])], dim=1)
+            verts = stages.lbs_forward_6d(self.smplx_model, smpl_params["pose_6d"].to(self._device),
+                                          shape.to(self._device, torch.float32))
+        else:
+            full, shape = self.smplx_model.full_pose(smpl_params)
+            verts = stages.lbs_vertices(self.smplx_model, full, shape)
         if getattr(self.cfg, "densify_smplx_verts", False):
             idx = self._fixed_idx
             if idx is None:
@@ -394,14 +404,22 @@ class Renderer(nn.Module):
         return rendered, gaussians
 
     # -- host-resident sequences ------------------------------------------------------------------
-    def render_sequence(self, triplane_features, cam_params, smpl_params, chunk: int = 8, out=None):
+    def render_sequence(self, triplane_features, cam_params, smpl_params, chunk: int = 8, out=None,
+                        out_dtype: torch.dtype = torch.float32, bgr: bool = False):
         """Render a [B,T] frame sequence whose triplane tokens live in (pinned) HOST memory and return the
         frames in pinned host memory: the stage-2 demo loop of the reference (main2.py:179-239) hands the
         renderer one clip after another and copies every frame back for the video sink.
 
         Frames are independent, so the sequence is cut into ``chunk``-frame pieces that flow through three
         streams: host->device copy of chunk k+1, render of chunk k, device->host copy of chunk k-1.
-        LBS for the whole sequence runs once up front (its inputs are a few KB per frame)."""
+        LBS for the whole sequence runs once up front (its inputs are a few KB per frame).
+
+        ``out_dtype=torch.uint8`` applies the demo's video sink on the device before the copy back
+        (``(frame * 255).astype(np.uint8)`` and, with ``bgr``, cv2's RGB2BGR; main2.py:351-353): a quarter of
+        the bytes leave the GPU (stages.frames_to_u8)."""
+        if out_dtype not in (torch.float32, torch.uint8):
+            raise ValueError("out_dtype must be torch.float32 or torch.uint8")
+        as_u8 = out_dtype == torch.uint8
         dev = self._device
         B, T = triplane_features.shape[0], triplane_features.shape[1]
         Fr = B * T
@@ -411,7 +429,9 @@ class Renderer(nn.Module):
         if tok.dtype != torch.float32:
             raise ValueError("triplane_features must be fp32")
         if out is None:
-            out = torch.empty(B, T, H, W, 3, dtype=torch.float32, pin_memory=True)
+            out = torch.empty(B, T, H, W, 3, dtype=out_dtype, pin_memory=True)
+        if out.dtype != out_dtype:
+            raise ValueError(f"out must be {out_dtype}")
         out_f = out.reshape(Fr, H, W, 3)
         main = torch.cuda.current_stream(dev)
         params = {k: v.to(dev, non_blocking=True) for k, v in smpl_params.items()}
@@ -452,6 +472,10 @@ class Renderer(nn.Module):
                            cameras=(view[f0:f1], full[f0:f1], tanfov[f0:f1]))
             ws = _workspace(dev)
             pending.append((k, ws.overflow.clone() if ws.overflow is not None else None))
+            if as_u8:
+                if st.get("img8") is None:
+                    st["img8"] = [torch.empty(chunk, H, W, 3, dtype=torch.uint8, device=dev) for _ in range(st["depth"])]
+                img = stages.frames_to_u8(img, bgr=bgr, out=st["img8"][slot][:n])
             rendered = torch.cuda.Event()
             rendered.record(main)
             with torch.cuda.stream(d2h):
@@ -470,7 +494,7 @@ class Renderer(nn.Module):
             _workspace(dev).capacity = 0
             img = _render_frames(g["xyz"], g["rot"], g["scale"], g["opacity"], g["color"], K[f0:f1], E[f0:f1], self.cfg,
                                  None, False, 1, True)
-            out_f[f0:f1].copy_(img)
+            out_f[f0:f1].copy_(stages.frames_to_u8(img, bgr=bgr) if as_u8 else img)
         return out
 
     def _seq_state(self, chunk, C, R, H, W, depth: int = 3):
@@ -482,7 +506,7 @@ class Renderer(nn.Module):
                   "tok": [torch.empty(chunk, C, 3 * R * R, device=dev) for _ in range(depth)],
                   "img": [torch.empty(chunk, H, W, 3, device=dev) for _ in range(depth)],
                   "proj": torch.empty(chunk, 3, R * R, 16, device=dev),
-                  "tok_free": [None] * depth, "img_free": [None] * depth}
+                  "img8": None, "tok_free": [None] * depth, "img_free": [None] * depth}
             self._seq = st
         else:
             st["tok_free"] = [None] * st["depth"]

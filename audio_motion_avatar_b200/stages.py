@@ -78,6 +78,66 @@ def lbs_forward(body: BodyModel, full_pose: torch.Tensor, shape_comp: torch.Tens
     return verts
 
 
+def pose_6d_from_decoder_heads(body_root_6d: torch.Tensor, body_6d: torch.Tensor, hand_6d: torch.Tensor,
+                               jaw_6d: torch.Tensor, leye_6d: torch.Tensor, reye_6d: torch.Tensor) -> torch.Tensor:
+    """[F,J,6] in smplx.SMPLX.forward's joint order (global, 21 body, jaw, leye, reye, 15 left hand, 15 right hand)
+    from the six 6D heads of the reference's SMPLXDecoder (smplx_decoder.py:106-127: `pred_hand_pose_6d` holds the left
+    hand first, then the right)."""
+    Fr = body_root_6d.shape[0]
+    hand = hand_6d.reshape(Fr, -1, 6)
+    nh = hand.shape[1] // 2
+    parts = [body_root_6d.reshape(Fr, 1, 6), body_6d.reshape(Fr, -1, 6), jaw_6d.reshape(Fr, 1, 6),
+             leye_6d.reshape(Fr, 1, 6), reye_6d.reshape(Fr, 1, 6), hand[:, :nh], hand[:, nh:]]
+    return torch.cat(parts, dim=1).contiguous()
+
+
+def lbs_forward_6d(body: BodyModel, pose_6d: torch.Tensor, shape_comp: torch.Tensor) -> torch.Tensor:
+    """Posed vertices [F,V,3] from 6D rotations [F,J,6] (amav_lbs_forward_6d).  The axis-angle pose_mean
+    of the body model cannot be composed with a rotation given as a matrix, so it must be zero (flat_hand_mean=True,
+    as the reference builds its model when it predicts the parameters).  Forward only."""
+    pose_6d = pose_6d.reshape(-1, body.J, 6)
+    Fr = int(pose_6d.shape[0])
+    if shape_comp.shape != (Fr, body.S):
+        raise ValueError("shape_comp must be [F,S]")
+    if torch.is_grad_enabled() and (pose_6d.requires_grad or shape_comp.requires_grad):
+        raise _lib.AmavError("lbs_forward_6d has no backward pass; use the axis-angle path for training")
+    if not hasattr(body, "_pose_mean_zero"):
+        body._pose_mean_zero = bool((body.pose_mean == 0).all().item())
+    if not body._pose_mean_zero:
+        raise ValueError("the 6D pose path needs a body model with pose_mean == 0 (flat_hand_mean=True)")
+    dev = body.device
+    pf = torch.empty(Fr, (body.J - 1) * 9, device=dev)
+    joints = torch.empty(Fr, body.J, 3, device=dev)
+    A = torch.empty(Fr, body.J, 12, device=dev)
+    v_posed = torch.empty(Fr, body.V, 3, device=dev)
+    verts = torch.empty(Fr, body.V, 3, device=dev)
+    call("amav_lbs_forward_6d", Fr, body.V, body.J, body.S, ptr(_f32c(pose_6d)), ptr(_f32c(shape_comp)),
+         ptr(body.v_template), ptr(body.shapedirs), ptr(body.posedirs), ptr(body.parents), ptr(body.J_template),
+         ptr(body.J_dirs), ptr(body.weights_T), ptr(pf), ptr(joints), ptr(A), ptr(v_posed), ptr(verts), stream_ptr())
+    return verts
+
+
+def frames_to_u8(frames: torch.Tensor, bgr: bool = False, out: Optional[torch.Tensor] = None,
+                 out_first: int = 0, out_step: int = 1) -> torch.Tensor:
+    """Video sink (amav_frames_to_u8; main2.py:226-239, :332-363): fp32 frames [F,H,W,3] -> uint8 [F,H,W,3] as
+    `(frame * 255).astype(np.uint8)`, optionally RGB->BGR.  With ``out`` [F_out,H,W,3] frame f is written to
+    out[out_first + f * out_step] (out_step = 2 interleaves two sequences the way the demo's combined_seq does)."""
+    if frames.dim() != 4 or frames.shape[-1] != 3 or frames.dtype != torch.float32:
+        raise ValueError("frames must be fp32 [F,H,W,3]")
+    Fr, H, W = int(frames.shape[0]), int(frames.shape[1]), int(frames.shape[2])
+    if out is None:
+        if out_first != 0 or out_step != 1:
+            raise ValueError("out_first / out_step need an explicit out buffer")
+        out = torch.empty(Fr, H, W, 3, dtype=torch.uint8, device=frames.device)
+    if out.dtype != torch.uint8 or out.dim() != 4 or tuple(out.shape[1:]) != (H, W, 3):
+        raise ValueError("out must be uint8 [F_out,H,W,3]")
+    if Fr and out_first + (Fr - 1) * out_step >= out.shape[0]:
+        raise ValueError("out has too few frames for out_first / out_step")
+    call("amav_frames_to_u8", Fr, H, W, ptr(frames), H * W * 3, ptr(out), H * W * 3, out_first, out_step,
+         int(bool(bgr)), stream_ptr())
+    return out
+
+
 def densify_gather(verts: torch.Tensor, par: torch.Tensor, wgt: torch.Tensor) -> torch.Tensor:
     """sites[f,i] = sum_k wgt[i,k] * verts[f, par[i,k]] (flattened SubdivideMeshes levels + subset,
     renderer.py:276-288).  par int32 [N,P], wgt fp32 [N,P]."""

@@ -380,7 +380,38 @@ def run_ours(args):
             img, _ = r(tokens, cams_d, None, params_d)               # this rank's shard, device-resident path
         torch.cuda.synchronize()
         line["e2e"]["max_abs_vs_device_path"] = float((out_h.to(dev) - img).abs().max().item())
-        del tok_h, out_h
+        del out_h
+        # the same call with the video sink on the device (uint8 frames leave the GPU), and the sink
+        # kernel alone over this shard's frames (HBM-bound: 12 bytes in + 3 out per pixel)
+        from audio_motion_avatar_b200 import stages as _st
+        out8 = torch.empty(1, Fr, size, size, 3, dtype=torch.uint8, pin_memory=True)
+        with torch.no_grad():
+            r.render_sequence(tok_h, cams, params, chunk=args.chunk, out=out8, out_dtype=torch.uint8)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                r.render_sequence(tok_h, cams, params, chunk=args.chunk, out=out8, out_dtype=torch.uint8)
+            torch.cuda.synchronize()
+            sec8 = time.perf_counter() - t0
+        flat = img.reshape(Fr, size, size, 3)
+        dst8 = torch.empty(Fr, size, size, 3, dtype=torch.uint8, device=dev)
+        for _ in range(3):
+            _st.frames_to_u8(flat, out=dst8)
+        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ea.record()
+        for _ in range(10):
+            _st.frames_to_u8(flat, out=dst8)
+        eb.record()
+        torch.cuda.synchronize()
+        sink_ms = ea.elapsed_time(eb) / 10
+        sink_bytes = flat.numel() * 5                                   # 4 B read + 1 B written per value
+        line["sink"] = {"e2e_u8_frames_per_s": Fr * steps / sec8, "d2h_bytes_per_step": out8.numel(),
+                        "bit_exact_vs_float_frames": bool(torch.equal(out8.reshape(Fr, size, size, 3).to(dev),
+                                                                      _st.frames_to_u8(flat))),
+                        "kernel_ms": sink_ms, "gbs": sink_bytes / (sink_ms * 1e-3) / 1e9,
+                        "frac_of_peak": sink_bytes / (sink_ms * 1e-3) / 1e9 / peaks()[0],
+                        "note": "this rank only; frames (1.5 GB) exceed L2"}
+        del tok_h, out8, dst8
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         fps, cores, sec = cpu_reference(1, 1, 0, size, N)

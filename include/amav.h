@@ -87,6 +87,17 @@ int amav_lbs_forward(int F, int V, int J, int S, const float *full_pose, const f
                      const float *weights_T, float *pose_feature, float *joints, float *A, float *v_posed,
                      float *verts, void *stream);
 
+/* Same forward with the pose given as pose_6d [F,J,6], the 6D rotation representation the SMPL-X parameter decoder's
+ * heads emit (src/models/smplx_decoder.py:106-127), in the joint order of full_pose.  R_j comes from
+ * Gram-Schmidt (pytorch3d.transforms.rotation_6d_to_matrix: the 6 numbers are the first two ROWS of R) instead of the
+ * reference's 6D -> matrix -> matrix_to_axis_angle -> batch_rodrigues round trip, which reproduces the same matrix up to
+ * fp32 rounding.  Only valid for a body model whose pose_mean is zero (flat_hand_mean); the host layer checks. */
+int amav_lbs_forward_6d(int F, int V, int J, int S, const float *pose_6d, const float *shape_comp,
+                        const float *v_template, const float *shapedirs, const float *posedirs,
+                        const int32_t *parents, const float *J_template, const float *J_dirs,
+                        const float *weights_T, float *pose_feature, float *joints, float *A, float *v_posed,
+                        float *verts, void *stream);
+
 /* sites[f][i] = sum_k wgt[i][k] * verts[f][par[i][k]], k < P (flattened SubdivideMeshes levels +
  * randperm subset, renderer.py:280-288).  P = 1 with wgt = 1 is the plain gather. */
 int amav_densify_gather(int F, int V, int N, int P, const float *verts, const int32_t *par,
@@ -246,6 +257,17 @@ int amav_image_loss_forward(int F, int H, int W, const float *img, const float *
                             void *stream);
 int amav_image_loss_backward(int F, int H, int W, const float *img, const float *gt, const float *maps,
                              const float *g_l1, const float *g_ssim, float *grad, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Video sink: the demo's host loop `(frame * 255).astype(np.uint8)`, cv2.cvtColor(RGB2BGR) and the
+ * even/odd interleave of two rendered sequences (src/main2.py:226-239, :332-363) as one pass on the device.
+ *   frames [F,H,W,3] fp32 (what render_batch returns), frame stride in floats;
+ *   out    uint8 [*,H,W,3], frame stride in bytes: input frame f lands in output frame out_first + f * out_step
+ *          (out_step = 2 with out_first = 0 / 1 interleaves two sequences); bgr != 0 swaps channels 0 and 2.
+ *   Conversion: fp32 product with 255, truncation toward zero (numpy astype), saturated to [0,255].
+ */
+int amav_frames_to_u8(int F, int H, int W, const float *frames, int64_t in_frame_stride, uint8_t *out,
+                      int64_t out_frame_stride, int out_first, int out_step, int bgr, void *stream);
 
 #ifdef __cplusplus
 }

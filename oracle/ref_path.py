@@ -170,6 +170,82 @@ def lbs_vertices(params: Dict[str, torch.Tensor], model: Dict[str, torch.Tensor]
     return verts
 
 
+# ----------------------------------------------------------------------------------------
+# 8f-3  SMPLXDecoder tail: 6D -> matrix -> axis-angle (src/models/smplx_decoder.py:106-127 calls
+# pytorch3d.transforms.rotation_6d_to_matrix / matrix_to_axis_angle; pytorch3d is absent here, PARITY UNPINNED:
+# restated from the package's published algorithm, checked by tests/test_oracle_invariants.py)
+# ----------------------------------------------------------------------------------------
+def rotation_6d_to_matrix(d6: torch.Tensor) -> torch.Tensor:
+    """pytorch3d.transforms.rotation_6d_to_matrix: Gram-Schmidt of the two 3-vectors; b1, b2, b3 are the ROWS."""
+    a1, a2 = d6[..., :3], d6[..., 3:]
+    b1 = torch.nn.functional.normalize(a1, dim=-1)
+    b2 = a2 - (b1 * a2).sum(-1, keepdim=True) * b1
+    b2 = torch.nn.functional.normalize(b2, dim=-1)
+    b3 = torch.cross(b1, b2, dim=-1)
+    return torch.stack((b1, b2, b3), dim=-2)
+
+
+def _sqrt_positive_part(x: torch.Tensor) -> torch.Tensor:
+    ret = torch.zeros_like(x)
+    pos = x > 0
+    ret[pos] = torch.sqrt(x[pos])
+    return ret
+
+
+def matrix_to_quaternion(matrix: torch.Tensor) -> torch.Tensor:
+    """pytorch3d.transforms.matrix_to_quaternion (real part first): four candidate quaternions, the one with the
+    largest denominator is taken; result standardised to a non-negative real part."""
+    batch = matrix.shape[:-2]
+    m00, m01, m02, m10, m11, m12, m20, m21, m22 = torch.unbind(matrix.reshape(batch + (9,)), dim=-1)
+    q_abs = _sqrt_positive_part(torch.stack([1.0 + m00 + m11 + m22, 1.0 + m00 - m11 - m22,
+                                             1.0 - m00 + m11 - m22, 1.0 - m00 - m11 + m22], dim=-1))
+    quat_by_rijk = torch.stack([
+        torch.stack([q_abs[..., 0] ** 2, m21 - m12, m02 - m20, m10 - m01], dim=-1),
+        torch.stack([m21 - m12, q_abs[..., 1] ** 2, m10 + m01, m02 + m20], dim=-1),
+        torch.stack([m02 - m20, m10 + m01, q_abs[..., 2] ** 2, m12 + m21], dim=-1),
+        torch.stack([m10 - m01, m20 + m02, m21 + m12, q_abs[..., 3] ** 2], dim=-1)], dim=-2)
+    flr = torch.tensor(0.1, dtype=q_abs.dtype)
+    cand = quat_by_rijk / (2.0 * q_abs[..., None].max(flr))
+    pick = torch.nn.functional.one_hot(q_abs.argmax(dim=-1), num_classes=4) > 0.5
+    out = cand[pick, :].reshape(batch + (4,))
+    return torch.where(out[..., 0:1] < 0, -out, out)
+
+
+def quaternion_to_axis_angle(q: torch.Tensor) -> torch.Tensor:
+    """pytorch3d.transforms.quaternion_to_axis_angle."""
+    norms = torch.norm(q[..., 1:], p=2, dim=-1, keepdim=True)
+    half = torch.atan2(norms, q[..., :1])
+    angles = 2 * half
+    small = angles.abs() < 1e-6
+    soa = torch.empty_like(angles)
+    soa[~small] = torch.sin(half[~small]) / angles[~small]
+    soa[small] = 0.5 - (angles[small] * angles[small]) / 48
+    return q[..., 1:] / soa
+
+
+def matrix_to_axis_angle(matrix: torch.Tensor) -> torch.Tensor:
+    return quaternion_to_axis_angle(matrix_to_quaternion(matrix))
+
+
+def params_from_pose_6d(pose_6d: torch.Tensor, betas: torch.Tensor, expression: torch.Tensor) -> Dict[str, torch.Tensor]:
+    """The reference's route for predicted poses: every joint's 6D head -> matrix -> axis-angle
+    (smplx_decoder.py:106-143), in the dict layout get_smpl_vertices reads (renderer.py:250-258).
+    pose_6d [F,55,6] in SMPLX.forward's joint order."""
+    Fr = pose_6d.shape[0]
+    aa = matrix_to_axis_angle(rotation_6d_to_matrix(pose_6d))              # [F,55,3]
+    return {"global_orient": aa[:, 0], "body_pose": aa[:, 1:22], "jaw_pose": aa[:, 22], "leye_pose": aa[:, 23],
+            "reye_pose": aa[:, 24], "left_hand_pose": aa[:, 25:40], "right_hand_pose": aa[:, 40:55],
+            "betas": betas.reshape(Fr, -1), "expression": expression.reshape(Fr, -1)}
+
+
+# ----------------------------------------------------------------------------------------
+# 8f-4  video sink of the demo (src/main2.py:351-353): (frame * 255).astype(np.uint8), optional cv2 RGB2BGR
+# ----------------------------------------------------------------------------------------
+def frames_to_u8(frames: np.ndarray, bgr: bool = False) -> np.ndarray:
+    u8 = (np.asarray(frames, dtype=np.float32) * 255).astype(np.uint8)
+    return u8[..., ::-1].copy() if bgr else u8
+
+
 def subdivide_vertices(verts: torch.Tensor, level_edges) -> torch.Tensor:
     """pytorch3d SubdivideMeshes on the vertices only: per level, append the mean of each edge's
     endpoints (``verts[:, edges].mean(dim=2)``) after the existing vertices (renderer.py:282-285)."""

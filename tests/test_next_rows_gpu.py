@@ -1,0 +1,104 @@
+"""SURVEY 8f-3 (6D pose straight into LBS) and 8f-4 (video sink) on the GPU vs the oracle's restatement of the
+reference route (smplx_decoder.py:106-127 -> renderer.py:261-274; main2.py:351-353)."""
+import numpy as np
+import pytest
+import torch
+
+from audio_motion_avatar_b200 import synthetic as S
+from oracle import ref_path as O
+from tests.test_renderer_gpu import make_cfg
+
+pytestmark = pytest.mark.gpu
+TIGHT = 5e-5
+
+
+def _pose_6d(Fr, seed):
+    g = torch.Generator().manual_seed(seed)
+    eye6 = torch.tensor([1.0, 0, 0, 0, 1.0, 0])
+    return eye6[None, None] + 0.35 * torch.randn(Fr, 55, 6, generator=g)
+
+
+def test_lbs_6d_matches_reference_route():
+    """6D -> Gram-Schmidt -> LBS on the device == 6D -> matrix -> axis-angle -> Rodrigues -> LBS (oracle)."""
+    from audio_motion_avatar_b200.stages import BodyModel, lbs_forward_6d, pose_6d_from_decoder_heads
+    model = S.make_body_model(seed=0)
+    body = BodyModel(model, "cuda:0")
+    Fr = 19
+    d6 = _pose_6d(Fr, 3)
+    g = torch.Generator().manual_seed(4)
+    betas, expr = torch.randn(Fr, 10, generator=g), 0.5 * torch.randn(Fr, 10, generator=g)
+    ref = O.lbs_vertices(O.params_from_pose_6d(d6, betas, expr), model)
+    # the decoder's six heads, packed the way SMPLXDecoder splits them
+    packed = pose_6d_from_decoder_heads(d6[:, 0], d6[:, 1:22].reshape(Fr, 126), d6[:, 25:55].reshape(Fr, 180),
+                                        d6[:, 22], d6[:, 23], d6[:, 24])
+    assert torch.equal(packed, d6)
+    verts = lbs_forward_6d(body, packed.cuda(), torch.cat([betas, expr], 1).cuda())
+    err = (verts.cpu() - ref).abs().max().item()
+    assert err < TIGHT, err
+
+
+def test_lbs_6d_rejects_pose_mean_and_grad():
+    from audio_motion_avatar_b200._lib import AmavError
+    from audio_motion_avatar_b200.stages import BodyModel, lbs_forward_6d
+    d6 = _pose_6d(2, 1).cuda()
+    shape = torch.zeros(2, 20, device="cuda")
+    with pytest.raises(ValueError):
+        lbs_forward_6d(BodyModel(S.make_body_model(seed=0, flat_hand_mean=False), "cuda:0"), d6, shape)
+    with pytest.raises(AmavError):
+        lbs_forward_6d(BodyModel(S.make_body_model(seed=0), "cuda:0"), d6.requires_grad_(True), shape)
+
+
+def test_renderer_accepts_pose_6d():
+    from audio_motion_avatar_b200.renderer import Renderer
+    H, W, C, R = 64, 48, 64, 16
+    model = S.make_body_model(seed=0)
+    r = Renderer(make_cfg(H, W, C, R), body_model=model)
+    d6 = _pose_6d(3, 7)
+    betas, expr = torch.zeros(3, 10), torch.zeros(3, 10)
+    pts = r.get_smpl_vertices({"pose_6d": d6.reshape(1, 3, 55, 6).cuda(), "betas": betas.cuda(), "expression": expr.cuda()})
+    ref = O.lbs_vertices(O.params_from_pose_6d(d6, betas, expr), model)
+    assert (pts.cpu() - ref).abs().max().item() < TIGHT
+
+
+@pytest.mark.parametrize("H,W", [(64, 48), (70, 45), (1, 3)])     # 70x45 and 1x3: H*W % 4 != 0, scalar instantiation
+@pytest.mark.parametrize("bgr", [False, True])
+def test_frames_to_u8_bit_exact(H, W, bgr):
+    from audio_motion_avatar_b200.stages import frames_to_u8
+    g = torch.Generator().manual_seed(H * W)
+    fr = torch.rand(5, H, W, 3, generator=g)
+    fr.view(-1)[:6] = torch.tensor([0.0, 1.0, 0.5, 254.999 / 255, 1.0 / 255, 0.99999994])
+    got = frames_to_u8(fr.cuda(), bgr=bgr).cpu().numpy()
+    assert np.array_equal(got, O.frames_to_u8(fr.numpy(), bgr=bgr))
+
+
+def test_frames_to_u8_interleaves_two_sequences():
+    """combined_seq of main2.py:328-331: even_seq[i], odd_seq[i], even_seq[i+1], ..."""
+    from audio_motion_avatar_b200.stages import frames_to_u8
+    g = torch.Generator().manual_seed(0)
+    a, b = torch.rand(3, 32, 40, 3, generator=g), torch.rand(3, 32, 40, 3, generator=g)
+    out = torch.zeros(6, 32, 40, 3, dtype=torch.uint8, device="cuda")
+    frames_to_u8(a.cuda(), out=out, out_first=0, out_step=2)
+    frames_to_u8(b.cuda(), out=out, out_first=1, out_step=2)
+    want = np.empty((6, 32, 40, 3), np.uint8)
+    want[0::2], want[1::2] = O.frames_to_u8(a.numpy()), O.frames_to_u8(b.numpy())
+    assert np.array_equal(out.cpu().numpy(), want)
+    with pytest.raises(ValueError):
+        frames_to_u8(a.cuda(), out=out, out_first=2, out_step=2)
+
+
+def test_render_sequence_uint8_equals_sink_of_float_frames():
+    from audio_motion_avatar_b200.renderer import Renderer
+    H, W, C, R, T = 96, 80, 64, 16, 5
+    model = S.make_body_model(seed=0)
+    r = Renderer(make_cfg(H, W, C, R), body_model=model)
+    r.gaussian_decoder.load_state_dict(S.make_decoder_weights(C, seed=1))
+    tokens = S.make_triplane_tokens(T, C, R, seed=2).reshape(1, T, C, 3 * R * R).pin_memory()
+    params, cams = S.make_pose_sequence(1, T, seed=2), S.make_cameras(1, T, H, W)
+    with torch.no_grad():
+        f32 = r.render_sequence(tokens, cams, params, chunk=2).clone()
+        u8 = r.render_sequence(tokens, cams, params, chunk=2, out_dtype=torch.uint8, bgr=True)
+        dev = r(tokens.cuda(), {k: v.cuda() for k, v in cams.items()}, None, {k: v.cuda() for k, v in params.items()})[0]
+    assert torch.equal(f32, dev.cpu())                             # the chunked host path renders the same frames
+    assert u8.dtype == torch.uint8 and u8.shape == (1, T, H, W, 3)
+    assert np.array_equal(u8.numpy(), O.frames_to_u8(f32.numpy(), bgr=True))
+    assert f32.min() < 0.5                                         # not a blank canvas

@@ -119,3 +119,27 @@ def test_weights_sum_and_sorted_lists():
     assert np.abs(out1["color"][0] - (1 - out1["final_T"])).max() < 1e-5
     r = binned["ranges"]
     assert ((r[:, 1] - r[:, 0]) >= out1["n_contrib"].reshape(H // 16, 16, W // 16, 16).max((1, 3)).reshape(-1)).all()
+
+
+# ---- 8f-3 / 8f-4: restatements of pytorch3d's rotation conversions and of the demo's uint8 sink ----
+def test_rotation_6d_and_axis_angle_round_trip():
+    """rotation_6d_to_matrix gives proper rotations whose first two rows span the inputs; matrix_to_axis_angle is
+    the inverse of smplx's Rodrigues (what the reference relies on between smplx_decoder.py:106 and lbs)."""
+    g = torch.Generator().manual_seed(0)
+    d6 = torch.randn(2000, 6, generator=g)
+    R = O.rotation_6d_to_matrix(d6)
+    assert (R @ R.transpose(-1, -2) - torch.eye(3)).abs().max().item() < 1e-5
+    assert (torch.det(R) - 1).abs().max().item() < 1e-5
+    assert (torch.nn.functional.normalize(d6[:, :3], dim=-1) - R[:, 0]).abs().max().item() < 1e-6
+    back = O.batch_rodrigues(O.matrix_to_axis_angle(R))
+    assert (back - R).abs().max().item() < 1e-5
+    aa = 0.8 * torch.randn(500, 3, generator=g)                       # angles below pi: the map is one-to-one
+    aa = aa * (aa.norm(dim=1, keepdim=True).clamp(max=3.0) / aa.norm(dim=1, keepdim=True))
+    assert (O.matrix_to_axis_angle(O.batch_rodrigues(aa)) - aa).abs().max().item() < 2e-4
+    assert torch.allclose(O.matrix_to_axis_angle(torch.eye(3)[None]), torch.zeros(1, 3), atol=1e-7)
+
+
+def test_frames_to_u8_known_answers():
+    x = np.array([[[[0.0, 1.0, 0.5], [1.0 / 255, 254.999 / 255, 0.25]]]], dtype=np.float32)
+    assert O.frames_to_u8(x).tolist() == [[[[0, 255, 127], [1, 254, 63]]]]
+    assert O.frames_to_u8(x, bgr=True).tolist() == [[[[127, 255, 0], [63, 254, 1]]]]
