@@ -79,7 +79,7 @@ def main():
         if rep.startswith("seq"):
             traffic_all = traffic
     open(f"profiles/r01_ncu_full_summary_{sfx}.txt", "w").write(text)
-    names = {"amav_splat_blend": "blend_kernel<0>", "amav_triplane_project": "project_kernel",
+    names = {"amav_splat_blend": "blend_kernel<0, 0>", "amav_triplane_project": "project_kernel",
              "amav_splat_preprocess": "preprocess_kernel", "amav_sample_decode": "sample_decode_kernel"}
     json.dump({"source": f"profiles/r01_ncu_full_summary_{sfx}.txt (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)",
                "workload": {"frames": 120, "gaussians": 100000, "size": 1024},
