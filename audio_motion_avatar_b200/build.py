@@ -21,6 +21,7 @@ SOURCES = [
     ("splat_preprocess_bwd.cu", []),
     ("triplane.cu", []),
     ("triplane_bwd.cu", []),
+    ("triplane_tm.cu", []),
     ("lbs.cu", []),
     ("lbs_bwd.cu", []),
     ("image_loss.cu", []),

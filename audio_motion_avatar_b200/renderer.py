@@ -359,12 +359,17 @@ class Renderer(nn.Module):
                 "color": color, "shs": color}
 
     def decode_gaussians(self, triplane_features, points, transl):
-        """Stages 1+2 for [F,C,3*R*R] tokens and [F,N,3] posed sites -> the ``gaussians`` dict."""
+        """Stages 1+2 for [F,C,3*R*R] tokens and [F,N,3] posed sites -> the ``gaussians`` dict.
+        ``cfg.triplane_token_major`` (extension): tokens are [F,3*R*R,C], the layout the upstream
+        transformer computes in before its permute+contiguous (transformers.py:1070-1073)."""
         C, R = int(self.cfg.triplane_feature_dim), int(self.cfg.triplane_resolution)
         W, b = self._decoder_wb()
+        tm = bool(getattr(self.cfg, "triplane_token_major", False))
         if torch.is_grad_enabled() and any(t.requires_grad for t in (triplane_features, points, transl, W, b)):
+            if tm:                                                 # the backward kernels are channel-major: pay the transposition
+                triplane_features = triplane_features.transpose(1, 2).contiguous()
             return stages.decode_gaussians_autograd(triplane_features, points, transl, W, b, C, R, float(self.cfg.radius))
-        proj = stages.triplane_project(triplane_features, W, C, R)
+        proj = stages.triplane_project(triplane_features, W, C, R, token_major=tm)
         return stages.sample_decode(proj, points, transl, W, b, C, R, float(self.cfg.radius))
 
     def forward(self, triplane_features, cam_params, smpl_tokens=None, smpl_params_gt=None, out=None):
@@ -392,7 +397,10 @@ class Renderer(nn.Module):
             raise ValueError("no SMPL-X parameters: pass smpl_params_gt or build the Renderer with a smpl_decoder "
                              "and cfg.predict_smplx_params=True")
         C, R = int(self.cfg.triplane_feature_dim), int(self.cfg.triplane_resolution)
-        tokens = triplane_features.reshape(B * T, C, 3 * R * R)
+        if getattr(self.cfg, "triplane_token_major", False):
+            tokens = triplane_features.reshape(B * T, 3 * R * R, C)
+        else:
+            tokens = triplane_features.reshape(B * T, C, 3 * R * R)
         if tokens.device != dev or tokens.dtype != torch.float32:
             tokens = tokens.to(dev, torch.float32)
         points = self.get_smpl_vertices(smpl_params)                                   # [F,N,3]

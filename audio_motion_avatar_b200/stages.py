@@ -162,9 +162,23 @@ def decoder_matrix(decoder) -> Tuple[torch.Tensor, torch.Tensor]:
 
 
 def triplane_project(tokens: torch.Tensor, weight: torch.Tensor, C: int, R: int,
-                     out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                     out: Optional[torch.Tensor] = None, token_major: bool = False) -> torch.Tensor:
     """tokens [F, C, 3*R*R] (channel-major, renderer.py:85-91; the frame stride may exceed C*3*R*R)
-    -> projected planes [F, 3, R*R, 16]."""
+    -> projected planes [F, 3, R*R, 16].  ``token_major``: tokens [F, 3*R*R, C], the layout the upstream
+    transformer computes in before its permute+contiguous (transformers.py:1070-1073)."""
+    if token_major:
+        if tokens.dim() != 3 or tokens.shape[1] != 3 * R * R or tokens.shape[2] != C:
+            raise ValueError(f"token-major tokens must be [F,{3 * R * R},{C}], got {tuple(tokens.shape)}")
+        if tokens.dtype != torch.float32 or not tokens.is_cuda:
+            raise _lib.AmavError("tokens must be CUDA fp32")
+        if tokens.stride(2) != 1 or tokens.stride(1) != C:
+            tokens = tokens.contiguous()
+        Fr = int(tokens.shape[0])
+        fstride = int(tokens.stride(0)) if Fr > 1 else C * 3 * R * R
+        if out is None:
+            out = torch.empty(Fr, 3, R * R, 16, device=tokens.device)
+        call("amav_triplane_project_tm", Fr, C, R, ctypes_ptr(tokens), fstride, ptr(_f32c(weight)), ptr(out), stream_ptr())
+        return out
     if tokens.dim() != 3 or tokens.shape[1] != C or tokens.shape[2] != 3 * R * R:
         raise ValueError(f"tokens must be [F,{C},{3 * R * R}], got {tuple(tokens.shape)}")
     if tokens.dtype != torch.float32 or not tokens.is_cuda:

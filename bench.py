@@ -412,6 +412,29 @@ def run_ours(args):
                         "frac_of_peak": sink_bytes / (sink_ms * 1e-3) / 1e9 / peaks()[0],
                         "note": "this rank only; frames (1.5 GB) exceed L2"}
         del tok_h, out8, dst8
+        # the projection fed in the producer's token-major layout [F, 3*R*R, C] (no permute+contiguous
+        # upstream) next to the channel-major one, same tokens, kernels alone
+        Cc, Rr = int(r.cfg.triplane_feature_dim), int(r.cfg.triplane_resolution)
+        tok_cm = tokens.reshape(Fr, Cc, 3 * Rr * Rr)
+        tok_tm = tok_cm.transpose(1, 2).contiguous()
+        Wd = r._decoder_wb()[0].detach().contiguous()
+        pj = torch.empty(Fr, 3, Rr * Rr, 16, device=dev)
+        res = {}
+        for name, tk, tmf in (("channel_major", tok_cm, False), ("token_major", tok_tm, True)):
+            for _ in range(3):
+                _st.triplane_project(tk, Wd, Cc, Rr, out=pj, token_major=tmf)
+            ea.record()
+            for _ in range(10):
+                _st.triplane_project(tk, Wd, Cc, Rr, out=pj, token_major=tmf)
+            eb.record()
+            torch.cuda.synchronize()
+            ms = ea.elapsed_time(eb) / 10
+            by = tk.numel() * 4 + pj.numel() * 4
+            res[name] = {"kernel_ms": ms, "gbs": by / (ms * 1e-3) / 1e9, "frac_of_peak": by / (ms * 1e-3) / 1e9 / peaks()[0]}
+        res["max_abs_difference"] = float((_st.triplane_project(tok_tm, Wd, Cc, Rr, token_major=True) -
+                                           _st.triplane_project(tok_cm, Wd, Cc, Rr)).abs().max().item())
+        line["producer_layout"] = res
+        del tok_tm, pj
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         fps, cores, sec = cpu_reference(1, 1, 0, size, N)

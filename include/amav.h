@@ -52,6 +52,15 @@ int64_t amav_launch_count(void);
 int amav_triplane_project(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
                           const float *weight, float *proj, void *stream);
 
+/* Same projection from the producer's own layout: tokens_tm [F, 3*R*R, C] token-major, i.e. the upstream
+ * transformer's hidden_states before its `.permute(0, 2, 1).contiguous()` (src/models/transformers.py:1070-1073; the
+ * residual it adds afterwards is added in the same layout).  Texel (p, t) of frame f is the C contiguous floats at
+ * tokens_tm[f][p*R*R + t]; frame stride in floats.  Output identical in layout to amav_triplane_project and equal up to
+ * fp32 summation order.  C % 64 == 0, (R*R) % 64 == 0.
+ */
+int amav_triplane_project_tm(int F, int C, int R, const float *tokens_tm, int64_t token_frame_stride,
+                             const float *weight, float *proj, void *stream);
+
 /* Stage 2: bilinear query of the projected triplane + xyz/bias terms + construct_gaussians
  * (renderer.py:292-317, :165-171, :319-346).
  *   points [F,N,3]  posed, pre-transl sites;  transl [F,3];  weight [14,3+3C]; bias [14]

@@ -102,3 +102,58 @@ def test_render_sequence_uint8_equals_sink_of_float_frames():
     assert u8.dtype == torch.uint8 and u8.shape == (1, T, H, W, 3)
     assert np.array_equal(u8.numpy(), O.frames_to_u8(f32.numpy(), bgr=True))
     assert f32.min() < 0.5                                         # not a blank canvas
+
+
+# ---- 8f-2: the projection from the producer's token-major layout ----
+@pytest.mark.parametrize("C,R,F", [(64, 16, 3), (512, 64, 2), (192, 16, 1)])
+def test_token_major_projection_matches_channel_major_and_oracle(C, R, F):
+    """amav_triplane_project_tm on tokens^T == amav_triplane_project on tokens (fp32 summation order only), and both
+    equal W_feat . tokens computed in float64."""
+    from audio_motion_avatar_b200.stages import decoder_matrix, triplane_project
+    g = torch.Generator().manual_seed(C + R)
+    tokens = torch.randn(F, C, 3 * R * R, generator=g)
+    Wd, _ = decoder_matrix(S.make_decoder_weights(C, seed=3))
+    cm = triplane_project(tokens.cuda(), Wd.cuda(), C, R)
+    tm_in = tokens.transpose(1, 2).contiguous().cuda()                       # [F, 3*R*R, C]
+    tm = triplane_project(tm_in, Wd.cuda(), C, R, token_major=True)
+    torch.cuda.synchronize()
+    assert tm.shape == cm.shape == (F, 3, R * R, 16)
+    slot_row = [3, 4, 5, 6, 0, 1, 2, 10, 7, 8, 9, -1, 11, 12, 13, -1]
+    ref = torch.zeros(F, 3, R * R, 16, dtype=torch.float64)
+    t64 = tokens.double().reshape(F, C, 3, R * R)
+    for s, row in enumerate(slot_row):
+        if row >= 0:
+            for p in range(3):
+                ref[:, p, :, s] = torch.einsum("c,fct->ft", Wd[row, 3 + p * C:3 + (p + 1) * C].double(), t64[:, :, p])
+    assert (tm.cpu().double() - ref).abs().max().item() < 2e-5
+    assert (tm - cm).abs().max().item() < 2e-5
+    assert torch.equal(tm[..., 11], torch.zeros_like(tm[..., 11])) and torch.equal(tm[..., 15], torch.zeros_like(tm[..., 15]))
+    # padded frame stride
+    if F > 1:
+        pad = torch.zeros(F, 3 * R * R + 8, C, device="cuda")
+        pad[:, :3 * R * R] = tm_in
+        assert torch.equal(triplane_project(pad[:, :3 * R * R], Wd.cuda(), C, R, token_major=True), tm)
+
+
+def test_renderer_token_major_equals_channel_major():
+    from audio_motion_avatar_b200.renderer import Renderer
+    H, W, C, R, T = 96, 80, 64, 16, 2
+    model = S.make_body_model(seed=0)
+    w = S.make_decoder_weights(C, seed=1)
+    tokens = S.make_triplane_tokens(T, C, R, seed=2)                          # [1,T,C,3RR]
+    params = {k: v.cuda() for k, v in S.make_pose_sequence(1, T, seed=2).items()}
+    cams = {k: v.cuda() for k, v in S.make_cameras(1, T, H, W).items()}
+    imgs = []
+    for tm in (False, True):
+        cfg = make_cfg(H, W, C, R)
+        cfg.triplane_token_major = tm
+        r = Renderer(cfg, body_model=model)
+        r.gaussian_decoder.load_state_dict(w)
+        tk = tokens.transpose(2, 3).contiguous() if tm else tokens
+        with torch.no_grad():
+            imgs.append(r(tk.cuda(), cams, None, params)[0])
+    d = (imgs[0] - imgs[1]).abs()
+    # 1e-6 attribute differences can move a (pixel, Gaussian) pair across the rasteriser's alpha >= 1/255 cut
+    assert (d > 1e-3).float().mean().item() <= 1e-4 and d.max().item() <= 1.0 / 255 + 1e-3
+    from tests.helpers import psnr
+    assert psnr(imgs[0].cpu(), imgs[1].cpu()) > 60
