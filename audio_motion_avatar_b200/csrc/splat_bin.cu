@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t *__res
 constexpr int SCAT_CHUNK = 2048;
 constexpr int SCAT_PER = SCAT_CHUNK / 256;
 
-__global__ void __launch_bounds__(256) scatter_entries(int N, int gx, int tiles, const float4 *__restrict__ geom,
+__global__ void __launch_bounds__(256, 4) scatter_entries(int N, int gx, int tiles, const float4 *__restrict__ geom,
                                                         const ushort4 *__restrict__ rect,
                                                         const uint32_t *__restrict__ tile_start,
                                                         uint32_t *__restrict__ tile_cursor,
@@ -125,10 +125,16 @@ __global__ void __launch_bounds__(256) scatter_entries(int N, int gx, int tiles,
     const int f = blockIdx.y;
     const int64_t tbase = (int64_t)f * tiles;
     ushort4 rc[SCAT_PER];
+    float depth[SCAT_PER];                                   // fetched up front: the loads overlap the histogram phases
 #pragma unroll
     for (int k = 0; k < SCAT_PER; ++k) {
         const int i = blockIdx.x * SCAT_CHUNK + k * 256 + threadIdx.x;
         rc[k] = i < N ? rect[(int64_t)f * N + i] : make_ushort4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int k = 0; k < SCAT_PER; ++k) {
+        const int i = blockIdx.x * SCAT_CHUNK + k * 256 + threadIdx.x;
+        depth[k] = (rc[k].z > rc[k].x && rc[k].w > rc[k].y) ? geom[3 * ((int64_t)f * N + i) + 2].z : 0.0f;
     }
     if (use_smem) {
         for (int t = threadIdx.x; t < tiles; t += 256) s_pos[t] = 0u;
@@ -138,9 +144,21 @@ __global__ void __launch_bounds__(256) scatter_entries(int N, int gx, int tiles,
             for (int y = rc[k].y; y < rc[k].w; ++y)
                 for (int x = rc[k].x; x < rc[k].z; ++x) atomicAdd(&s_pos[y * gx + x], 1u);
         __syncthreads();
-        for (int t = threadIdx.x; t < tiles; t += 256) {
-            const uint32_t c = s_pos[t];
-            if (c) s_pos[t] = tile_start[tbase + t] + atomicAdd(tile_cursor + tbase + t, c);
+        // four tiles per thread and step: the tile_start loads and the cursor atomics of a step are in flight together
+        for (int t0 = threadIdx.x; t0 < tiles; t0 += 4 * 256) {
+            uint32_t c[4], st[4], old[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int t = t0 + u * 256;
+                c[u] = t < tiles ? s_pos[t] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) st[u] = c[u] ? tile_start[tbase + t0 + u * 256] : 0u;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) old[u] = c[u] ? atomicAdd(tile_cursor + tbase + t0 + u * 256, c[u]) : 0u;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (c[u]) s_pos[t0 + u * 256] = st[u] + old[u];
         }
         __syncthreads();
     }
@@ -148,8 +166,7 @@ __global__ void __launch_bounds__(256) scatter_entries(int N, int gx, int tiles,
     for (int k = 0; k < SCAT_PER; ++k) {
         if (rc[k].z <= rc[k].x || rc[k].w <= rc[k].y) continue;
         const uint32_t i = (uint32_t)(blockIdx.x * SCAT_CHUNK + k * 256 + threadIdx.x);
-        const float depth = geom[3 * ((int64_t)f * N + i) + 2].z;
-        const uint64_t e = ((uint64_t)__float_as_uint(depth) << 32) | (uint64_t)i;
+        const uint64_t e = ((uint64_t)__float_as_uint(depth[k]) << 32) | (uint64_t)i;
         for (int y = rc[k].y; y < rc[k].w; ++y)
             for (int x = rc[k].x; x < rc[k].z; ++x) {
                 const int t = y * gx + x;

@@ -56,7 +56,7 @@ int amav_triplane_project(int F, int C, int R, const float *tokens, int64_t toke
  * transformer's hidden_states before its `.permute(0, 2, 1).contiguous()` (src/models/transformers.py:1070-1073; the
  * residual it adds afterwards is added in the same layout).  Texel (p, t) of frame f is the C contiguous floats at
  * tokens_tm[f][p*R*R + t]; frame stride in floats.  Output identical in layout to amav_triplane_project and equal up to
- * fp32 summation order.  C % 64 == 0, (R*R) % 64 == 0.
+ * fp32 summation order.  C % 64 == 0, (R*R) % 128 == 0.
  */
 int amav_triplane_project_tm(int F, int C, int R, const float *tokens_tm, int64_t token_frame_stride,
                              const float *weight, float *proj, void *stream);
