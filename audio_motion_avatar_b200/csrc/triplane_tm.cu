@@ -5,11 +5,11 @@
 // is: same output (projected planes [F,3,R*R,16], triplane.cu) from tokens_tm [F, 3*R*R, C].
 //
 //   CTA = 128 texels of one plane x all C channels, 256 threads.  A texel's C channels are contiguous (2 KB), so a
-//   [128 texels x 64 channels] chunk is 256-byte row segments: cp.async (16 bytes per request, L1 bypassed) drops them
-//   into a double-buffered shared-memory tile with a row stride of 68 floats while the previous chunk is in the FMAs --
-//   no staging registers.  The FMAs run with lane = texel (4 texels per lane, LDS.128 of 4 channels at a time:
+//   [128 texels x 32 channels] chunk is 128-byte row segments: cp.async (16 bytes per request, L1 bypassed) drops them
+//   into a four-slot ring of shared-memory tiles (row stride 36 floats), three chunks in flight while one is in the FMAs
+//   -- no staging registers.  The FMAs run with lane = texel (4 texels per lane, LDS.128 of 4 channels at a time:
 //   4*lane + c covers all 32 banks per quarter-warp) and the weights broadcast from smem [C][16], the work decomposition
-//   of project_kernel: warp w owns 8 of the chunk's 64 channels, 4 texels x 14 accumulators per lane, cross-warp
+//   of project_kernel: warp w owns 4 of the chunk's 32 channels, 4 texels x 14 accumulators per lane, cross-warp
 //   reduction through shared memory at the end.  HBM-bound: the 25.2 MB/frame of tokens are read once.
 #include "common.cuh"
 
@@ -19,10 +19,14 @@ __constant__ int c_slot_row_tm[16] = {3, 4, 5, 6, 0, 1, 2, 10, 7, 8, 9, -1, 11, 
 
 constexpr int TM_THREADS = 256;
 constexpr int TM_TEX = 128;            // texels per CTA
-constexpr int TM_KC = 64;              // channels per staged chunk
+constexpr int TM_KC = 32;              // channels per staged chunk
+constexpr int TM_STAGES = 4;           // staged chunks in shared memory (TM_STAGES - 1 in flight during the FMAs)
 constexpr int TM_LD = TM_KC + 4;       // row stride of the staged chunk (floats; rows stay 16-byte aligned)
 constexpr int TM_WARPS = TM_THREADS / 32;
-constexpr int TM_CPW = TM_KC / TM_WARPS;   // channels per warp per chunk (8 = two float4)
+constexpr int TM_CPW = TM_KC / TM_WARPS;   // channels per warp per chunk (4 = one float4)
+constexpr int TM_RPT = TM_KC / 4;          // 16-byte requests per texel row of a chunk
+constexpr int TM_RSTEP = TM_THREADS / TM_RPT;   // texel rows covered by one request per thread
+constexpr int TM_REQ = TM_TEX / TM_RSTEP;       // requests per thread and chunk
 constexpr int TM_TPL = TM_TEX / 32;        // texels per lane
 constexpr int TM_TILE = TM_TEX * TM_LD;    // floats per staged chunk
 
@@ -32,7 +36,8 @@ __device__ __forceinline__ void cp_async16(float *smem_dst, const float *gmem_sr
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __global__ void __launch_bounds__(TM_THREADS, 2)
 project_tm_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame_stride,
@@ -40,20 +45,27 @@ project_tm_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame
 {
     extern __shared__ float4 s_dyn_tm[];
     float *s_w = reinterpret_cast<float *>(s_dyn_tm);                // [C][16]
-    float *s_t = s_w + (size_t)C * 16;                               // 2 x [TM_TEX][TM_LD], later red[8][14][TM_TEX]
+    float *s_t = s_w + (size_t)C * 16;                               // TM_STAGES x [TM_TEX][TM_LD], later red[8][14][TM_TEX]
     const int tiles_per_plane = R2 / TM_TEX;
     const int tile = blockIdx.x % tiles_per_plane;
     const int p = (blockIdx.x / tiles_per_plane) % 3;
     const int f = blockIdx.x / (3 * tiles_per_plane);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    // this thread's share of a chunk: 8 requests of 16 bytes = texel rows (threadIdx.x >> 4) + 16 q, channels 4 * (threadIdx.x & 15)
-    const int lrow = threadIdx.x >> 4, lcol = (threadIdx.x & 15) * 4;
+    // this thread's share of a chunk: TM_REQ requests of 16 bytes = texel rows lrow + TM_RSTEP q, channels lcol..lcol+3
+    const int lrow = threadIdx.x / TM_RPT, lcol = (threadIdx.x % TM_RPT) * 4;
     const float *src = tokens + (int64_t)f * frame_stride + ((int64_t)p * R2 + (int64_t)tile * TM_TEX + lrow) * C + lcol;
     float *dst = s_t + lrow * TM_LD + lcol;
+    const int nchunks = C / TM_KC;
 #pragma unroll
-    for (int q = 0; q < TM_TEX / 16; ++q) cp_async16(dst + 16 * q * TM_LD, src + (int64_t)(16 * q) * C);
-    cp_async_commit();
+    for (int st = 0; st < TM_STAGES - 1; ++st) {
+        if (st < nchunks) {
+#pragma unroll
+            for (int q = 0; q < TM_REQ; ++q)
+                cp_async16(dst + st * TM_TILE + TM_RSTEP * q * TM_LD, src + (int64_t)(TM_RSTEP * q) * C + st * TM_KC);
+        }
+        cp_async_commit();                                           // one group per chunk slot, empty or not
+    }
 
     for (int i = threadIdx.x; i < C * 16; i += TM_THREADS) {
         const int c = i >> 4, s = i & 15;
@@ -68,16 +80,21 @@ project_tm_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame
         for (int o = 0; o < 14; ++o) acc[t][o] = 0.0f;
 
     int buf = 0;
-    for (int c0 = 0; c0 < C; c0 += TM_KC, buf ^= 1) {
-        cp_async_wait_all();
-        __syncthreads();                 // chunk c0 (and, first time, the weights) visible; the other buffer is free
-        if (c0 + TM_KC < C) {
-            float *dn = dst + (buf ^ 1) * TM_TILE;
+    for (int k = 0; k < nchunks; ++k) {
+        cp_async_wait<TM_STAGES - 2>();  // chunk k has landed (this thread's requests) ...
+        __syncthreads();                 // ... everybody's; first time also the weights; buffer of chunk k-1 is free
+        {
+            const int kn = k + TM_STAGES - 1;
+            if (kn < nchunks) {
+                float *dn = dst + (kn % TM_STAGES) * TM_TILE;
 #pragma unroll
-            for (int q = 0; q < TM_TEX / 16; ++q) cp_async16(dn + 16 * q * TM_LD, src + (int64_t)(16 * q) * C + c0 + TM_KC);
+                for (int q = 0; q < TM_REQ; ++q)
+                    cp_async16(dn + TM_RSTEP * q * TM_LD, src + (int64_t)(TM_RSTEP * q) * C + kn * TM_KC);
+            }
             cp_async_commit();
         }
         const float *tb = s_t + buf * TM_TILE + warp * TM_CPW;
+        const int c0 = k * TM_KC;
 #pragma unroll
         for (int h = 0; h < TM_CPW / 4; ++h) {
             float4 tv[TM_TPL];
@@ -97,7 +114,9 @@ project_tm_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame
                 }
             }
         }
+        buf = buf + 1 == TM_STAGES ? 0 : buf + 1;
     }
+    cp_async_wait<0>();
     __syncthreads();
     // cross-warp (channel slice) reduction through shared memory: red[warp][o][texel]
     float *s_red = s_t;
@@ -130,12 +149,12 @@ extern "C" int amav_triplane_project_tm(int F, int C, int R, const float *tokens
 {
     AMAV_CHECK_ARG(F >= 0 && C > 0 && R > 0, "bad dims");
     AMAV_CHECK_ARG((R * R) % TM_TEX == 0, "R*R must be a multiple of 128");
-    AMAV_CHECK_ARG(C % TM_KC == 0, "C must be a multiple of 64");
+    AMAV_CHECK_ARG(C % 64 == 0, "C must be a multiple of 64");
     AMAV_CHECK_ARG(token_frame_stride >= (int64_t)C * 3 * R * R, "frame stride too small");
     if (F == 0) return AMAV_OK;
     AMAV_CHECK_ARG(tokens_tm && weight && proj, "null buffer");
     AMAV_CHECK_ARG(((uintptr_t)tokens_tm & 15) == 0 && (token_frame_stride & 3) == 0, "tokens must be 16-byte aligned");
-    const size_t tile_floats = 2 * (size_t)TM_TILE, red_floats = (size_t)TM_WARPS * 14 * TM_TEX;
+    const size_t tile_floats = (size_t)TM_STAGES * TM_TILE, red_floats = (size_t)TM_WARPS * 14 * TM_TEX;
     const size_t smem = ((size_t)C * 16 + (tile_floats > red_floats ? tile_floats : red_floats)) * sizeof(float);
     AMAV_CHECK_ARG(smem <= 200 * 1024, "C too large for the shared-memory weight tile");
     cudaFuncSetAttribute(project_tm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
