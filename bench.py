@@ -63,10 +63,16 @@ def parse():
     return ap.parse_args()
 
 
+def subdivide_steps(ngauss):
+    """Level-2 subdivision of the 10,475-vertex body has 167,420 vertices; the 500k-Gaussian stress configuration
+    (BASELINE.json configs[4]) draws its sites from level 3 (669,644)."""
+    return 2 if ngauss <= 167_420 else 3
+
+
 def make_cfg(size, ngauss, device):
     return SimpleNamespace(device=device, triplane_resolution=R, triplane_feature_dim=C, radius=1.4,
                            smplx_model_path=None, flat_hand_mean=True, num_expression_coeffs=10,
-                           upsample_triplane=False, densify_smplx_verts=ngauss != 10475, subdivide_steps=2,
+                           upsample_triplane=False, densify_smplx_verts=ngauss != 10475, subdivide_steps=subdivide_steps(ngauss),
                            predict_smplx_params=False, no_point_refiner=True, use_gaussian_splatting=True,
                            image_size=(size, size), rgb=True, sh_degree=3, num_gaussians=ngauss)
 
@@ -195,7 +201,7 @@ def cpu_reference(frames_per_step, steps, warmup, size, ngauss, seed=0):
     w = S.make_decoder_weights(C, seed=0)
     levels, idx = None, None
     if ngauss != 10475:
-        levels = S.subdivision_levels(10475, model["faces"].numpy(), 2)
+        levels = S.subdivision_levels(10475, model["faces"].numpy(), subdivide_steps(ngauss))
         nd = 10475 + sum(len(e) for e in levels)
         idx = torch.randperm(nd, generator=torch.Generator().manual_seed(seed))[:ngauss]
     tokens = S.make_triplane_tokens(frames_per_step, C, R, seed=seed)[0]
@@ -231,8 +237,10 @@ def run_reference(args):
 
 
 def workload_name(args):
+    which = "configs[1]" if (args.frames, args.gaussians, args.size) == (FRAMES, NGAUSS, SIZE) else \
+        "configs[4] sizes, secondary line" if (args.gaussians, args.size) == (500_000, 2048) else "non-default sizes, secondary line"
     return (f"{args.frames}-frame audio-driven sequence, {args.gaussians} Gaussians, {args.size}x{args.size}, "
-            f"triplane 3x{R}x{R}x{C} fp32 per frame, 55-joint synthetic SMPL-X body (BASELINE.json configs[1])")
+            f"triplane 3x{R}x{R}x{C} fp32 per frame, 55-joint synthetic SMPL-X body (BASELINE.json {which})")
 
 
 def run_ours(args):
