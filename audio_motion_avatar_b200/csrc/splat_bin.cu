@@ -209,11 +209,76 @@ __device__ __forceinline__ void bitonic_sort(Ptr a, int n, int logP)
     }
 }
 
+// Bitonic sort of a bucket that does not fit the shared-memory tile (n > CH = 2^LC entries, in place in global memory
+// g): the same network as bitonic_sort, but every compare-exchange step whose stride is below CH runs on CH-entry
+// chunks staged in shared memory (padded with +inf keys, which the network leaves in place); only the
+// O(log^2(n / CH)) steps with a stride of CH or more touch global memory.  A 32768-entry bucket makes 3 passes over
+// global memory instead of 120.
+template <int LC>
+__device__ void bitonic_sort_large(uint64_t *__restrict__ g, uint64_t *s, int n, int logP)
+{
+    constexpr int CH = 1 << LC;
+    const int nch = (n + CH - 1) >> LC;
+    const int half = 1 << (logP - 1);
+    auto load = [&](int c) {
+        const int base = c << LC;
+        for (int i = threadIdx.x; i < CH; i += blockDim.x) s[i] = base + i < n ? g[base + i] : ~0ull;
+        __syncthreads();
+    };
+    auto store = [&](int c) {
+        const int base = c << LC;
+        for (int i = threadIdx.x; i < CH; i += blockDim.x)
+            if (base + i < n) g[base + i] = s[i];
+        __syncthreads();
+    };
+    for (int c = 0; c < nch; ++c) {                      // merges up to size CH: each chunk sorted on its own
+        load(c);
+        bitonic_sort(s, CH, LC);
+        store(c);
+    }
+    for (int lk = LC + 1; lk <= logP; ++lk) {            // merge size k = 2^lk > CH
+        const int lhk = lk - 1, hk = 1 << lhk;
+        for (int i = threadIdx.x; i < half; i += blockDim.x) {            // flip step, across chunks
+            const int blk = i >> lhk, r = i & (hk - 1);
+            const int lo = (blk << lk) + r, hi = (blk << lk) + (2 * hk - 1) - r;
+            if (hi < n) {
+                const uint64_t x = g[lo], y = g[hi];
+                if (y < x) { g[lo] = y; g[hi] = x; }
+            }
+        }
+        __syncthreads();
+        for (int lj = lhk - 1; lj >= LC; --lj) {         // half-cleaners whose stride spans chunks
+            const int j = 1 << lj;
+            for (int i = threadIdx.x; i < half; i += blockDim.x) {
+                const int lo = ((i >> lj) << (lj + 1)) + (i & (j - 1)), hi = lo + j;
+                if (hi < n) {
+                    const uint64_t x = g[lo], y = g[hi];
+                    if (y < x) { g[lo] = y; g[hi] = x; }
+                }
+            }
+            __syncthreads();
+        }
+        for (int c = 0; c < nch; ++c) {                  // the remaining half-cleaners (strides CH/2 .. 1) per chunk
+            load(c);
+            for (int lj = LC - 1; lj >= 0; --lj) {
+                const int j = 1 << lj;
+                for (int i = threadIdx.x; i < CH / 2; i += blockDim.x) {
+                    const int lo = ((i >> lj) << (lj + 1)) + (i & (j - 1)), hi = lo + j;
+                    const uint64_t x = s[lo], y = s[hi];
+                    if (y < x) { s[lo] = y; s[hi] = x; }
+                }
+                __syncthreads();
+            }
+            store(c);
+        }
+    }
+}
+
 // Two instantiations of the per-tile sort share one body:
 //   sort_tiles<256, 4096, 16>    buckets of up to 4096 entries: 48 KB of smem, 4 CTAs per SM;
 //   sort_tiles<1024, 16384, 64>  buckets of 4097..16384 entries (512x512 training views, 500k-Gaussian close-ups):
 //                                192 KB of smem, one CTA per SM; larger buckets still: bitonic network in place in
-//                                global memory (L2).
+//                                global memory with every stride below 16384 done on chunks in shared memory.
 constexpr int SORT_SMALL_T = 256, SORT_SMALL_CAP = 4096, SORT_SMALL_POP = 16;
 constexpr int SORT_LARGE_T = 1024, SORT_LARGE_CAP = 16384, SORT_LARGE_POP = 64;
 constexpr int SORT_MAX_BIN = 48;                     // a depth bin fuller than this sends the tile to the bitonic network
@@ -360,7 +425,8 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
             __syncthreads();                                       // the previous tile is done with shared memory
             if (n > CAP) {
                 uint64_t *g = entries + s;
-                bitonic_sort(g, n, logP);
+                static_assert((CAP & (CAP - 1)) == 0, "CAP must be a power of two");
+                bitonic_sort_large<31 - __builtin_clz(CAP)>(g, s_ent, n, logP);
                 for (int i = tid; i < n; i += T) point_list[s + i] = (int32_t)(uint32_t)g[i];
                 continue;
             }

@@ -78,11 +78,12 @@ def test_splat_empty_and_degenerate():
     assert torch.all(o0["color"] == 0.0)
 
 
-@pytest.mark.parametrize("N,min_largest", [(12000, 8192), (24000, 16384)])
+@pytest.mark.parametrize("N,min_largest", [(12000, 8192), (24000, 16384), (50000, 32768)])
 def test_splat_large_buckets(N, min_largest):
     # Thousands of Gaussians stacked on a few tiles.  12000: buckets of 4097..16384 entries (the 1024-thread
     # shared-memory instantiation of the per-tile sort) next to small ones; 24000: a bucket above 16384 entries
-    # (bitonic network in place in global memory).
+    # (bitonic network in place in global memory, strides below 16384 on chunks in shared memory: one merge level
+    # across two chunks); 50000: above 32768 (two cross-chunk merge levels incl. a cross-chunk half-cleaner).
     W, H = 32, 32
     sc = random_scene(N, W, H, seed=5, spread=0.05, smin=0.002, smax=0.004)
     sc["opac"] *= 0.02
