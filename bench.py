@@ -351,6 +351,12 @@ def run_ours(args):
                 "frac": per_stage[top]["frac"], "traffic": traffic, "peak_source": peak_src,
                 "share_of_step": round(stages_ms[top] / ms_per_step, 4), "stages": per_stage,
                 "entries_D": D, "entries_per_frame": D // max(Fr, 1)}
+    if "amav_splat_blend" in stages_ms and stages_ms["amav_splat_blend"] > 0:
+        # the blend's true limiter is instruction issue, so its rate is also given in (pixel, list entry) pairs:
+        # every list entry of a tile is a candidate for its 256 pixels (upstream evaluates exactly these pairs until the
+        # tile saturates); ncu's issue-slot utilisation of the kernel is in profiles/ (83 % of peak, IPC 3.3 of 4)
+        roofline["blend_pixel_entry_pairs_per_s"] = round(D * 256 / (stages_ms["amav_splat_blend"] * 1e-3), 0)
+        roofline["blend_note"] = "compute-bound (FP32 issue), HBM fraction reported because the contract asks for hbm|tensor"
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
