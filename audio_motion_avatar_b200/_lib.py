@@ -38,6 +38,7 @@ _SIGS = {
     "amav_triplane_project_backward": [c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p],
     "amav_densify_gather_backward": [c_int, c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
     "amav_lbs_backward": [c_int, c_int, c_int, c_int] + [c_void_p] * 16 + [c_void_p],
+    "amav_lbs_backward_6d": [c_int, c_int, c_int, c_int] + [c_void_p] * 16 + [c_void_p],
     "amav_camera_setup": [c_int, c_void_p, c_void_p, c_int, c_int, c_double, c_double, c_void_p, c_void_p, c_void_p, c_void_p],
     "amav_image_loss_forward": [c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
     "amav_image_loss_backward": [c_int, c_int, c_int] + [c_void_p] * 6 + [c_void_p],

@@ -173,6 +173,9 @@ __global__ void __launch_bounds__(PBB_THREADS) pose_blend_bwd_kernel(int F, int 
 }
 
 // One CTA (64 threads) per frame.
+// SIXD: full_pose is [F,J,6] (the 6D heads, amav_lbs_forward_6d) and d_full_pose [F,J,6]: Gram-Schmidt backward in
+// place of the Rodrigues backward.
+template <bool SIXD>
 __global__ void __launch_bounds__(64) chain_bwd_kernel(int J, int S, const float *__restrict__ full_pose,
                                                        const float *__restrict__ shape_comp,
                                                        const float *__restrict__ J_template,
@@ -188,6 +191,20 @@ __global__ void __launch_bounds__(64) chain_bwd_kernel(int J, int S, const float
     __shared__ int s_par[MAXJ];
     const int t = threadIdx.x;
     if (t < J) {
+        if (SIXD) {
+            const float *d6 = full_pose + ((int64_t)f * J + t) * 6;
+            const float a1x = d6[0], a1y = d6[1], a1z = d6[2], a2x = d6[3], a2y = d6[4], a2z = d6[5];
+            const float n1 = fmaxf(sqrtf(a1x * a1x + a1y * a1y + a1z * a1z), 1e-12f);
+            const float b1x = a1x / n1, b1y = a1y / n1, b1z = a1z / n1;
+            const float dt = b1x * a2x + b1y * a2y + b1z * a2z;
+            const float ux = a2x - dt * b1x, uy = a2y - dt * b1y, uz = a2z - dt * b1z;
+            const float n2 = fmaxf(sqrtf(ux * ux + uy * uy + uz * uz), 1e-12f);
+            const float b2x = ux / n2, b2y = uy / n2, b2z = uz / n2;
+            s_R[t][0] = b1x; s_R[t][1] = b1y; s_R[t][2] = b1z;
+            s_R[t][3] = b2x; s_R[t][4] = b2y; s_R[t][5] = b2z;
+            s_R[t][6] = b1y * b2z - b1z * b2y; s_R[t][7] = b1z * b2x - b1x * b2z; s_R[t][8] = b1x * b2y - b1y * b2x;
+            s_rod[t][0] = n1; s_rod[t][1] = n2; s_rod[t][2] = dt;
+        } else {
         const float rx = full_pose[((int64_t)f * J + t) * 3], ry = full_pose[((int64_t)f * J + t) * 3 + 1],
                     rz = full_pose[((int64_t)f * J + t) * 3 + 2];
         const float ex = rx + 1e-8f, ey = ry + 1e-8f, ez = rz + 1e-8f;
@@ -200,6 +217,7 @@ __global__ void __launch_bounds__(64) chain_bwd_kernel(int J, int S, const float
         s_R[t][3] = sn * z + oc * (x * y); s_R[t][4] = 1.0f + oc * (-(x * x + z * z)); s_R[t][5] = sn * (-x) + oc * (y * z);
         s_R[t][6] = sn * (-y) + oc * (x * z); s_R[t][7] = sn * x + oc * (y * z); s_R[t][8] = 1.0f + oc * (-(x * x + y * y));
         s_rod[t][0] = x; s_rod[t][1] = y; s_rod[t][2] = z; s_rod[t][3] = sn; s_rod[t][4] = cs; s_rod[t][5] = angle;
+        }
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             float a = J_template[3 * t + k];
@@ -273,6 +291,26 @@ __global__ void __launch_bounds__(64) chain_bwd_kernel(int J, int S, const float
         float dR[9];
 #pragma unroll
         for (int k = 0; k < 9; ++k) dR[k] = s_dR[t][k] + (t > 0 ? d_pose_feature[(int64_t)f * (J - 1) * 9 + (t - 1) * 9 + k] : 0.0f);
+        if (SIXD) {
+            // R rows: b1 = a1/|a1|, b2 = u/|u| with u = a2 - (b1.a2) b1, b3 = b1 x b2
+            const float n1 = s_rod[t][0], n2 = s_rod[t][1], dt = s_rod[t][2];
+            const float b1x = s_R[t][0], b1y = s_R[t][1], b1z = s_R[t][2], b2x = s_R[t][3], b2y = s_R[t][4], b2z = s_R[t][5];
+            const float *d6 = full_pose + ((int64_t)f * J + t) * 6;
+            const float a2x = d6[3], a2y = d6[4], a2z = d6[5];
+            // b3 = b1 x b2: d/db1 = b2 x g3, d/db2 = g3 x b1
+            float gb1x = dR[0] + (b2y * dR[8] - b2z * dR[7]), gb1y = dR[1] + (b2z * dR[6] - b2x * dR[8]),
+                  gb1z = dR[2] + (b2x * dR[7] - b2y * dR[6]);
+            const float gb2x = dR[3] + (dR[7] * b1z - dR[8] * b1y), gb2y = dR[4] + (dR[8] * b1x - dR[6] * b1z),
+                        gb2z = dR[5] + (dR[6] * b1y - dR[7] * b1x);
+            const float p2 = b2x * gb2x + b2y * gb2y + b2z * gb2z;
+            const float gux = (gb2x - b2x * p2) / n2, guy = (gb2y - b2y * p2) / n2, guz = (gb2z - b2z * p2) / n2;
+            const float q = b1x * gux + b1y * guy + b1z * guz;
+            gb1x -= q * a2x + dt * gux; gb1y -= q * a2y + dt * guy; gb1z -= q * a2z + dt * guz;
+            const float p1 = b1x * gb1x + b1y * gb1y + b1z * gb1z;
+            float *o = d_full_pose + ((int64_t)f * J + t) * 6;
+            o[0] = (gb1x - b1x * p1) / n1; o[1] = (gb1y - b1y * p1) / n1; o[2] = (gb1z - b1z * p1) / n1;
+            o[3] = gux - b1x * q; o[4] = guy - b1y * q; o[5] = guz - b1z * q;
+        } else {
         const float x = s_rod[t][0], y = s_rod[t][1], z = s_rod[t][2], sn = s_rod[t][3], cs = s_rod[t][4], angle = s_rod[t][5];
         const float oc = 1.0f - cs;
         // R = I + sn K + oc M, K = [[0,-z,y],[z,0,-x],[-y,x,0]], M = K K
@@ -291,6 +329,7 @@ __global__ void __launch_bounds__(64) chain_bwd_kernel(int J, int S, const float
         o[0] = dnx / angle + dth_t * (rx + 1e-8f) / angle;
         o[1] = dny / angle + dth_t * (ry + 1e-8f) / angle;
         o[2] = dnz / angle + dth_t * (rz + 1e-8f) / angle;
+        }
     }
     // joints = J_template + J_dirs . shape
     for (int s = t; s < S; s += blockDim.x) {
@@ -316,7 +355,7 @@ extern "C" int amav_densify_gather_backward(int F, int V, int N, int P, const fl
     return AMAV_OK;
 }
 
-extern "C" int amav_lbs_backward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
+static int lbs_backward_impl(bool sixd, int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
                                  const float *shapedirs, const float *posedirs, const int32_t *parents,
                                  const float *J_template, const float *J_dirs, const float *weights_T, const float *A,
                                  const float *v_posed, const float *d_verts, float *d_v_posed, float *d_A,
@@ -339,9 +378,33 @@ extern "C" int amav_lbs_backward(int F, int V, int J, int S, const float *full_p
     const int ksplit = (4 * AMAV_SM_COUNT + (int)(gb.x * gb.y) - 1) / (int)(gb.x * gb.y);
     gb.z = ksplit < 1 ? 1 : (ksplit > 8 ? 8 : ksplit);
     pose_blend_bwd_kernel<<<gb, PBB_THREADS, smem, stream>>>(F, V, S, K, d_v_posed, shapedirs, posedirs, d_pose_feature, d_shape);
-    chain_bwd_kernel<<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, d_A, d_pose_feature,
-                                           d_full_pose, d_shape);
+    if (sixd)
+        chain_bwd_kernel<true><<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, d_A,
+                                                     d_pose_feature, d_full_pose, d_shape);
+    else
+        chain_bwd_kernel<false><<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, d_A,
+                                                      d_pose_feature, d_full_pose, d_shape);
     amav_count_launches(2);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
+}
+
+extern "C" int amav_lbs_backward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
+                                 const float *shapedirs, const float *posedirs, const int32_t *parents,
+                                 const float *J_template, const float *J_dirs, const float *weights_T, const float *A,
+                                 const float *v_posed, const float *d_verts, float *d_v_posed, float *d_A,
+                                 float *d_pose_feature, float *d_full_pose, float *d_shape, void *stream)
+{
+    return lbs_backward_impl(false, F, V, J, S, full_pose, shape_comp, shapedirs, posedirs, parents, J_template, J_dirs, weights_T, A,
+                             v_posed, d_verts, d_v_posed, d_A, d_pose_feature, d_full_pose, d_shape, stream);
+}
+
+extern "C" int amav_lbs_backward_6d(int F, int V, int J, int S, const float *pose_6d, const float *shape_comp,
+                                 const float *shapedirs, const float *posedirs, const int32_t *parents,
+                                 const float *J_template, const float *J_dirs, const float *weights_T, const float *A,
+                                 const float *v_posed, const float *d_verts, float *d_v_posed, float *d_A,
+                                 float *d_pose_feature, float *d_pose_6d, float *d_shape, void *stream)
+{
+    return lbs_backward_impl(true, F, V, J, S, pose_6d, shape_comp, shapedirs, posedirs, parents, J_template, J_dirs, weights_T, A,
+                             v_posed, d_verts, d_v_posed, d_A, d_pose_feature, d_pose_6d, d_shape, stream);
 }

@@ -303,11 +303,11 @@ class Renderer(nn.Module):
 
         A dict that carries ``pose_6d`` [..., J, 6] (stages.pose_6d_from_decoder_heads: the SMPL-X parameter decoder's
         6D heads, smplx_decoder.py:106-127) instead of the axis-angle keys goes through amav_lbs_forward_6d, without the
-        reference's matrix -> axis-angle -> Rodrigues round trip (forward only)."""
+        reference's matrix -> axis-angle -> Rodrigues round trip (gradients by amav_lbs_backward_6d)."""
         if "pose_6d" in smpl_params:
             shape = torch.cat([smpl_params["betas"].reshape(-1, smpl_params["betas"].shape[-1]),
                                smpl_params["expression"].reshape(-1, smpl_params["expression"].shape[-1])], dim=1)
-            verts = stages.lbs_forward_6d(self.smplx_model, smpl_params["pose_6d"].to(self._device),
+            verts = stages.lbs_vertices_6d(self.smplx_model, smpl_params["pose_6d"].to(self._device),
                                           shape.to(self._device, torch.float32))
         else:
             full, shape = self.smplx_model.full_pose(smpl_params)

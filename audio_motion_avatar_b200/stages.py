@@ -91,16 +91,15 @@ def pose_6d_from_decoder_heads(body_root_6d: torch.Tensor, body_6d: torch.Tensor
     return torch.cat(parts, dim=1).contiguous()
 
 
-def lbs_forward_6d(body: BodyModel, pose_6d: torch.Tensor, shape_comp: torch.Tensor) -> torch.Tensor:
+def lbs_forward_6d(body: BodyModel, pose_6d: torch.Tensor, shape_comp: torch.Tensor, return_aux: bool = False):
     """Posed vertices [F,V,3] from 6D rotations [F,J,6] (amav_lbs_forward_6d).  The axis-angle pose_mean
     of the body model cannot be composed with a rotation given as a matrix, so it must be zero (flat_hand_mean=True,
-    as the reference builds its model when it predicts the parameters).  Forward only."""
+    as the reference builds its model when it predicts the parameters).  Plain forward; ``lbs_vertices_6d`` is the
+    autograd-aware call."""
     pose_6d = pose_6d.reshape(-1, body.J, 6)
     Fr = int(pose_6d.shape[0])
     if shape_comp.shape != (Fr, body.S):
         raise ValueError("shape_comp must be [F,S]")
-    if torch.is_grad_enabled() and (pose_6d.requires_grad or shape_comp.requires_grad):
-        raise _lib.AmavError("lbs_forward_6d has no backward pass; use the axis-angle path for training")
     if not hasattr(body, "_pose_mean_zero"):
         body._pose_mean_zero = bool((body.pose_mean == 0).all().item())
     if not body._pose_mean_zero:
@@ -114,7 +113,43 @@ def lbs_forward_6d(body: BodyModel, pose_6d: torch.Tensor, shape_comp: torch.Ten
     call("amav_lbs_forward_6d", Fr, body.V, body.J, body.S, ptr(_f32c(pose_6d)), ptr(_f32c(shape_comp)),
          ptr(body.v_template), ptr(body.shapedirs), ptr(body.posedirs), ptr(body.parents), ptr(body.J_template),
          ptr(body.J_dirs), ptr(body.weights_T), ptr(pf), ptr(joints), ptr(A), ptr(v_posed), ptr(verts), stream_ptr())
+    if return_aux:
+        return verts, {"pose_feature": pf, "joints": joints, "A": A, "v_posed": v_posed}
     return verts
+
+
+class Lbs6dFunction(torch.autograd.Function):
+    """(pose_6d [F,J,6], shape_comp [F,S]) -> posed vertices [F,V,3]; gradients by amav_lbs_backward_6d."""
+
+    @staticmethod
+    def forward(ctx, body, pose_6d, shape_comp):
+        verts, aux = lbs_forward_6d(body, pose_6d, shape_comp, return_aux=True)
+        ctx.body = body
+        ctx.save_for_backward(pose_6d, shape_comp, aux["A"], aux["v_posed"])
+        return verts
+
+    @staticmethod
+    def backward(ctx, d_verts):
+        body = ctx.body
+        pose_6d, shape_comp, A, v_posed = ctx.saved_tensors
+        Fr, dev = int(A.shape[0]), body.device
+        d_v_posed = torch.empty(Fr, body.V, 3, device=dev)
+        d_A = torch.zeros(Fr, body.J, 12, device=dev)
+        d_pf = torch.zeros(Fr, (body.J - 1) * 9, device=dev)
+        d_pose = torch.empty(Fr, body.J, 6, device=dev)
+        d_shape = torch.zeros(Fr, body.S, device=dev)
+        call("amav_lbs_backward_6d", Fr, body.V, body.J, body.S, ptr(_f32c(pose_6d)), ptr(_f32c(shape_comp)),
+             ptr(body.shapedirs), ptr(body.posedirs), ptr(body.parents), ptr(body.J_template), ptr(body.J_dirs),
+             ptr(body.weights_T), ptr(A), ptr(v_posed), ptr(_f32c(d_verts)), ptr(d_v_posed), ptr(d_A), ptr(d_pf),
+             ptr(d_pose), ptr(d_shape), stream_ptr())
+        return None, d_pose.reshape(pose_6d.shape), d_shape
+
+
+def lbs_vertices_6d(body: BodyModel, pose_6d: torch.Tensor, shape_comp: torch.Tensor) -> torch.Tensor:
+    """Autograd-aware 6D LBS: the plain forward when nothing requires a gradient."""
+    if torch.is_grad_enabled() and (pose_6d.requires_grad or shape_comp.requires_grad):
+        return Lbs6dFunction.apply(body, pose_6d.reshape(-1, body.J, 6), shape_comp)
+    return lbs_forward_6d(body, pose_6d, shape_comp)
 
 
 def frames_to_u8(frames: torch.Tensor, bgr: bool = False, out: Optional[torch.Tensor] = None,

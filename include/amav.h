@@ -100,7 +100,8 @@ int amav_lbs_forward(int F, int V, int J, int S, const float *full_pose, const f
  * heads emit (src/models/smplx_decoder.py:106-127), in the joint order of full_pose.  R_j comes from
  * Gram-Schmidt (pytorch3d.transforms.rotation_6d_to_matrix: the 6 numbers are the first two ROWS of R) instead of the
  * reference's 6D -> matrix -> matrix_to_axis_angle -> batch_rodrigues round trip, which reproduces the same matrix up to
- * fp32 rounding.  Only valid for a body model whose pose_mean is zero (flat_hand_mean); the host layer checks. */
+ * fp32 rounding.  Only valid for a body model whose pose_mean is zero (flat_hand_mean); the host layer checks.
+ * Backward: amav_lbs_backward_6d. */
 int amav_lbs_forward_6d(int F, int V, int J, int S, const float *pose_6d, const float *shape_comp,
                         const float *v_template, const float *shapedirs, const float *posedirs,
                         const int32_t *parents, const float *J_template, const float *J_dirs,
@@ -244,6 +245,15 @@ int amav_triplane_project_backward(int F, int C, int R, const float *d_proj, con
  *   A, v_posed: the forward's work buffers (amav_lbs_forward); d_v_posed [F,V,3] scratch;
  *   d_A [F,J,12] and d_pose_feature [F,(J-1)*9] scratch, MUST be zeroed by the caller.
  */
+/* amav_lbs_backward_6d: the same backward for the 6D pose entry (amav_lbs_forward_6d): pose_6d [F,J,6] in,
+ * d_pose_6d [F,J,6] out (overwritten) through the Gram-Schmidt construction instead of Rodrigues -- the gradient the
+ * reference gets by autograd through rotation_6d_to_matrix -> matrix_to_axis_angle -> batch_rodrigues
+ * (smplx_decoder.py:106-127), i.e. what reaches the SMPL-X parameter decoder in stage-2 training. */
+int amav_lbs_backward_6d(int F, int V, int J, int S, const float *pose_6d, const float *shape_comp,
+                         const float *shapedirs, const float *posedirs, const int32_t *parents,
+                         const float *J_template, const float *J_dirs, const float *weights_T, const float *A,
+                         const float *v_posed, const float *d_verts, float *d_v_posed, float *d_A,
+                         float *d_pose_feature, float *d_pose_6d, float *d_shape, void *stream);
 int amav_densify_gather_backward(int F, int V, int N, int P, const float *d_sites, const int32_t *par,
                                  const float *wgt, float *d_verts, void *stream);
 int amav_lbs_backward(int F, int V, int J, int S, const float *full_pose, const float *shape_comp,
