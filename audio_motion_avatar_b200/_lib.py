@@ -36,6 +36,7 @@ _SIGS = {
     "amav_splat_bin": [ctypes.POINTER(SplatDims)] + [c_void_p] * 6 + [c_int64, c_void_p, c_void_p],
     "amav_sample_decode_backward": [c_int, c_int, c_int, c_int, c_float] + [c_void_p] * 13 + [c_void_p],
     "amav_triplane_project_backward": [c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p],
+    "amav_triplane_project_backward_tm": [c_int, c_int, c_int, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p],
     "amav_densify_gather_backward": [c_int, c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
     "amav_lbs_backward": [c_int, c_int, c_int, c_int] + [c_void_p] * 16 + [c_void_p],
     "amav_lbs_backward_6d": [c_int, c_int, c_int, c_int] + [c_void_p] * 16 + [c_void_p],

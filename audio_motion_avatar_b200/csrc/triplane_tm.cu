@@ -30,6 +30,7 @@ constexpr int TM_REQ = TM_TEX / TM_RSTEP;       // requests per thread and chunk
 constexpr int TM_TPL = TM_TEX / 32;        // texels per lane
 constexpr int TM_TILE = TM_TEX * TM_LD;    // floats per staged chunk
 
+__device__ __forceinline__ float4 ldcs4(const float *p) { return __ldcs(reinterpret_cast<const float4 *>(p)); }
 __device__ __forceinline__ void cp_async16(float *smem_dst, const float *gmem_src)
 {
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
@@ -142,6 +143,104 @@ project_tm_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame
     reinterpret_cast<float4 *>(out)[half * 2 + 1] = make_float4(r[4], r[5], r[6], r[7]);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Backward of the token-major projection (autograd of the five Linear heads on the feature columns, in the producer's
+// layout): d_tokens_tm[f][p*R2+t][c] = sum_slot W[row(slot)][3+p*C+c] * d_proj[f][p][t][slot] and
+// d_weight[row(slot)][3+p*C+c] += sum_{f,t} d_proj[f][p][t][slot] * tokens_tm[f][p*R2+t][c].
+// Both: CTA = TB_TEX texels of one plane, thread = (texel half, float4 channel column), the d_proj tile broadcast from
+// shared memory, 4 channels x 14 slots of weights (tokens kernel) or accumulators (weight kernel) in registers; a
+// texel's C channels leave / arrive as one contiguous row.
+constexpr int TB_THREADS = 256;
+constexpr int TB_TEX = 128;
+constexpr int TB_COLS = 128;           // float4 channel columns handled per pass (C = 512: one pass)
+
+__global__ void __launch_bounds__(TB_THREADS)
+project_tm_bwd_tokens_kernel(int C, int R2, const float *__restrict__ d_proj, const float *__restrict__ weight, int ldw,
+                             float *__restrict__ d_tokens, int64_t frame_stride, int accumulate)
+{
+    __shared__ float4 s_dp[TB_TEX * 4];                              // [texel][16]
+    const int tiles_per_plane = R2 / TB_TEX;
+    const int tile = blockIdx.x % tiles_per_plane;
+    const int p = (blockIdx.x / tiles_per_plane) % 3;
+    const int f = blockIdx.x / (3 * tiles_per_plane);
+    const float4 *dp = reinterpret_cast<const float4 *>(d_proj) + (((int64_t)f * 3 + p) * R2 + (int64_t)tile * TB_TEX) * 4;
+    for (int i = threadIdx.x; i < TB_TEX * 4; i += TB_THREADS) s_dp[i] = dp[i];
+    __syncthreads();
+    const int half = threadIdx.x / TB_COLS, col0 = threadIdx.x % TB_COLS;
+    float *dst = d_tokens + (int64_t)f * frame_stride + ((int64_t)p * R2 + (int64_t)tile * TB_TEX) * C;
+    for (int col = col0; col < C / 4; col += TB_COLS) {
+        float w[4][14];                                              // [channel of the float4][compact slot]
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int s = 0; s < 16; ++s) {
+                const int row = c_slot_row_tm[s];
+                if (row >= 0) w[j][s < 11 ? s : s - 1] = weight[(int64_t)row * ldw + 3 + p * C + 4 * col + j];
+            }
+        for (int t = half * (TB_TEX / 2); t < (half + 1) * (TB_TEX / 2); ++t) {
+            const float4 d0 = s_dp[4 * t], d1 = s_dp[4 * t + 1], d2 = s_dp[4 * t + 2], d3 = s_dp[4 * t + 3];
+            const float d[14] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w, d2.x, d2.y, d2.z, d3.x, d3.y, d3.z};
+            float o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float a = 0.0f;
+#pragma unroll
+                for (int s = 0; s < 14; ++s) a = fmaf(w[j][s], d[s], a);
+                o[j] = a;
+            }
+            float4 *q = reinterpret_cast<float4 *>(dst + (int64_t)t * C) + col;
+            if (accumulate) {
+                const float4 old = *q;
+                o[0] += old.x; o[1] += old.y; o[2] += old.z; o[3] += old.w;
+            }
+            *q = make_float4(o[0], o[1], o[2], o[3]);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(TB_THREADS)
+project_tm_bwd_weight_kernel(int C, int R2, const float *__restrict__ d_proj, const float *__restrict__ tokens,
+                             int64_t frame_stride, float *__restrict__ d_weight, int ldw)
+{
+    __shared__ float4 s_dp[TB_TEX * 4];                              // [texel][16]
+    const int tiles_per_plane = R2 / TB_TEX;
+    const int tile = blockIdx.x % tiles_per_plane;
+    const int p = (blockIdx.x / tiles_per_plane) % 3;
+    const int f = blockIdx.x / (3 * tiles_per_plane);
+    const float4 *dp = reinterpret_cast<const float4 *>(d_proj) + (((int64_t)f * 3 + p) * R2 + (int64_t)tile * TB_TEX) * 4;
+    for (int i = threadIdx.x; i < TB_TEX * 4; i += TB_THREADS) s_dp[i] = dp[i];
+    __syncthreads();
+    const int half = threadIdx.x / TB_COLS, col0 = threadIdx.x % TB_COLS;
+    const float *src = tokens + (int64_t)f * frame_stride + ((int64_t)p * R2 + (int64_t)tile * TB_TEX) * C;
+    for (int col = col0; col < C / 4; col += TB_COLS) {
+        float acc[4][14];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int s = 0; s < 14; ++s) acc[j][s] = 0.0f;
+        for (int t = half * (TB_TEX / 2); t < (half + 1) * (TB_TEX / 2); ++t) {
+            const float4 x = ldcs4(src + (int64_t)t * C + 4 * col);
+            const float4 d0 = s_dp[4 * t], d1 = s_dp[4 * t + 1], d2 = s_dp[4 * t + 2], d3 = s_dp[4 * t + 3];
+            const float d[14] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w, d2.x, d2.y, d2.z, d3.x, d3.y, d3.z};
+            const float xv[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int s = 0; s < 14; ++s) acc[j][s] = fmaf(xv[j], d[s], acc[j][s]);
+        }
+        // one reduction per (CTA half, channel, slot): 2 x 56 per column into the [14, 3+3C] gradient
+#pragma unroll
+        for (int s = 0; s < 16; ++s) {
+            const int row = c_slot_row_tm[s];
+            if (row < 0) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                atomicAdd(d_weight + (int64_t)row * ldw + 3 + p * C + 4 * col + j, acc[j][s < 11 ? s : s - 1]);
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" int amav_triplane_project_tm(int F, int C, int R, const float *tokens_tm, int64_t token_frame_stride,
@@ -163,5 +262,36 @@ extern "C" int amav_triplane_project_tm(int F, int C, int R, const float *tokens
     project_tm_kernel<<<(unsigned)grid, TM_THREADS, smem, (cudaStream_t)stream>>>(C, R * R, tokens_tm, token_frame_stride,
                                                                                   weight, 3 + 3 * C, proj);
     AMAV_CHECK_LAUNCH();
+    return AMAV_OK;
+}
+
+extern "C" int amav_triplane_project_backward_tm(int F, int C, int R, const float *d_proj, const float *tokens_tm,
+                                                 int64_t token_frame_stride, const float *weight, float *d_tokens_tm,
+                                                 int64_t d_token_frame_stride, int accumulate_tokens, float *d_weight,
+                                                 void *stream_)
+{
+    AMAV_CHECK_ARG(F >= 0 && C > 0 && R > 0, "bad dims");
+    AMAV_CHECK_ARG((R * R) % TB_TEX == 0, "R*R must be a multiple of 128");
+    AMAV_CHECK_ARG(C % 64 == 0, "C must be a multiple of 64");
+    if (F == 0) return AMAV_OK;
+    AMAV_CHECK_ARG(d_proj && weight, "null buffer");
+    AMAV_CHECK_ARG(((uintptr_t)d_proj & 15) == 0, "d_proj must be 16-byte aligned");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t grid = (int64_t)F * 3 * (R * R / TB_TEX);
+    AMAV_CHECK_ARG(grid < ((int64_t)1 << 31), "too many tiles");
+    if (d_tokens_tm) {
+        AMAV_CHECK_ARG(d_token_frame_stride >= (int64_t)C * 3 * R * R && (d_token_frame_stride & 3) == 0 &&
+                       ((uintptr_t)d_tokens_tm & 15) == 0, "bad d_tokens stride / alignment");
+        project_tm_bwd_tokens_kernel<<<(unsigned)grid, TB_THREADS, 0, stream>>>(C, R * R, d_proj, weight, 3 + 3 * C, d_tokens_tm,
+                                                                               d_token_frame_stride, accumulate_tokens);
+        AMAV_CHECK_LAUNCH();
+    }
+    if (d_weight) {
+        AMAV_CHECK_ARG(tokens_tm && token_frame_stride >= (int64_t)C * 3 * R * R && (token_frame_stride & 3) == 0 &&
+                       ((uintptr_t)tokens_tm & 15) == 0, "bad tokens stride / alignment");
+        project_tm_bwd_weight_kernel<<<(unsigned)grid, TB_THREADS, 0, stream>>>(C, R * R, d_proj, tokens_tm, token_frame_stride,
+                                                                               d_weight, 3 + 3 * C);
+        AMAV_CHECK_LAUNCH();
+    }
     return AMAV_OK;
 }

@@ -366,9 +366,8 @@ class Renderer(nn.Module):
         W, b = self._decoder_wb()
         tm = bool(getattr(self.cfg, "triplane_token_major", False))
         if torch.is_grad_enabled() and any(t.requires_grad for t in (triplane_features, points, transl, W, b)):
-            if tm:                                                 # the backward kernels are channel-major: pay the transposition
-                triplane_features = triplane_features.transpose(1, 2).contiguous()
-            return stages.decode_gaussians_autograd(triplane_features, points, transl, W, b, C, R, float(self.cfg.radius))
+            return stages.decode_gaussians_autograd(triplane_features, points, transl, W, b, C, R, float(self.cfg.radius),
+                                                    token_major=tm)
         proj = stages.triplane_project(triplane_features, W, C, R, token_major=tm)
         return stages.sample_decode(proj, points, transl, W, b, C, R, float(self.cfg.radius))
 

@@ -272,33 +272,37 @@ def sample_decode_backward(proj, points, weight, bias, grads: Dict[str, Optional
     return d_proj, d_points, d_transl, d_wb
 
 
-def triplane_project_backward(d_proj, tokens, weight, C: int, R: int, want_tokens: bool = True, want_weight: bool = True):
-    """d_proj [F,3,R*R,16] -> (d_tokens [F,C,3*R*R] or None, d_weight [14,3+3C] feature columns or None)."""
+def triplane_project_backward(d_proj, tokens, weight, C: int, R: int, want_tokens: bool = True, want_weight: bool = True,
+                              token_major: bool = False):
+    """d_proj [F,3,R*R,16] -> (d_tokens [F,C,3*R*R] ([F,3*R*R,C] when ``token_major``) or None, d_weight [14,3+3C]
+    feature columns or None)."""
     Fr = int(d_proj.shape[0])
     dev = d_proj.device
-    d_tokens = torch.empty(Fr, C, 3 * R * R, device=dev) if want_tokens else None
+    shape = (Fr, 3 * R * R, C) if token_major else (Fr, C, 3 * R * R)
+    d_tokens = torch.empty(shape, device=dev) if want_tokens else None
     d_weight = torch.zeros(14, 3 + 3 * C, device=dev) if want_weight else None
     tok_ptr, fstride = None, C * 3 * R * R
     if want_weight:
-        if tokens.stride(2) != 1 or tokens.stride(1) != 3 * R * R:
+        if tokens.stride(2) != 1 or tokens.stride(1) != shape[2]:
             tokens = tokens.contiguous()
         tok_ptr = ctypes_ptr(tokens)
         fstride = int(tokens.stride(0)) if Fr > 1 else C * 3 * R * R
-    call("amav_triplane_project_backward", Fr, C, R, ptr(d_proj), tok_ptr, fstride, ptr(_f32c(weight)), ptr(d_tokens),
-         C * 3 * R * R, 0, ptr(d_weight), stream_ptr())
+    call("amav_triplane_project_backward_tm" if token_major else "amav_triplane_project_backward", Fr, C, R, ptr(d_proj),
+         tok_ptr, fstride, ptr(_f32c(weight)), ptr(d_tokens), C * 3 * R * R, 0, ptr(d_weight), stream_ptr())
     return d_tokens, d_weight
 
 
 class DecodeFunction(torch.autograd.Function):
-    """tokens [F,C,3R^2], points [F,N,3], transl [F,3], weight [14,3+3C], bias [14] -> (xyz, scale, rot, opacity, color):
+    """tokens [F,C,3R^2] ([F,3R^2,C] when ``token_major``), points [F,N,3], transl [F,3], weight [14,3+3C], bias [14] -> (xyz, scale, rot, opacity, color):
     project-then-sample forward, and its hand-written backward (no [F,N,1536] feature tensor in either direction)."""
 
     @staticmethod
-    def forward(ctx, tokens, points, transl, weight, bias, C, R, radius):
-        proj = triplane_project(tokens, weight.detach(), C, R)
+    def forward(ctx, tokens, points, transl, weight, bias, C, R, radius, token_major=False):
+        proj = triplane_project(tokens, weight.detach(), C, R, token_major=token_major)
         g = sample_decode(proj, points, transl, weight.detach(), bias.detach(), C, R, radius)
         ctx.save_for_backward(tokens, points, weight, bias, proj)
         ctx.dims = (C, R, radius)
+        ctx.token_major = bool(token_major)
         return g["xyz"], g["scale"], g["rot"], g["opacity"], g["color"]
 
     @staticmethod
@@ -311,17 +315,20 @@ class DecodeFunction(torch.autograd.Function):
             C, R, radius, want_points=need_pts)
         d_tokens = d_weight = None
         if need_tok or need_w:
-            d_tokens, d_weight = triplane_project_backward(d_proj, tokens, weight, C, R, want_tokens=need_tok, want_weight=need_w)
+            d_tokens, d_weight = triplane_project_backward(d_proj, tokens, weight, C, R, want_tokens=need_tok, want_weight=need_w,
+                                                           token_major=ctx.token_major)
             if d_weight is not None:
                 d_weight[:, :3] = d_wb[:, :3]
             if d_tokens is not None and d_tokens.shape != tokens.shape:
                 d_tokens = d_tokens.reshape(tokens.shape)
         return (d_tokens, d_points, d_transl.reshape(-1, 3) if need_tr else None, d_weight,
-                d_wb[:, 3].contiguous() if need_b else None, None, None, None)
+                d_wb[:, 3].contiguous() if need_b else None, None, None, None, None)
 
 
-def decode_gaussians_autograd(tokens, points, transl, weight, bias, C: int, R: int, radius: float) -> Dict[str, torch.Tensor]:
-    xyz, scale, rot, opacity, color = DecodeFunction.apply(tokens, points, transl, weight, bias, int(C), int(R), float(radius))
+def decode_gaussians_autograd(tokens, points, transl, weight, bias, C: int, R: int, radius: float,
+                              token_major: bool = False) -> Dict[str, torch.Tensor]:
+    xyz, scale, rot, opacity, color = DecodeFunction.apply(tokens, points, transl, weight, bias, int(C), int(R), float(radius),
+                                                           bool(token_major))
     return {"xyz": xyz, "scale": scale, "rot": rot, "opacity": opacity, "color": color, "shs": color}
 
 

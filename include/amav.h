@@ -236,6 +236,12 @@ int amav_triplane_project_backward(int F, int C, int R, const float *d_proj, con
                                    int64_t token_frame_stride, const float *weight, float *d_tokens,
                                    int64_t d_token_frame_stride, int accumulate_tokens, float *d_weight, void *stream);
 
+/* amav_triplane_project_backward_tm: the same two products for the producer's token-major layout (amav_triplane_project_tm):
+ * tokens_tm, d_tokens_tm [F, 3*R*R, C].  C % 64 == 0, (R*R) % 128 == 0. */
+int amav_triplane_project_backward_tm(int F, int C, int R, const float *d_proj, const float *tokens_tm,
+                                      int64_t token_frame_stride, const float *weight, float *d_tokens_tm,
+                                      int64_t d_token_frame_stride, int accumulate_tokens, float *d_weight, void *stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Stage 3 backward (autograd of smplx.lbs.lbs and of the densify gather in the reference, renderer.py:261-288;
  * exercised when the SMPL-X parameters are predicted, i.e. stage-2 training).

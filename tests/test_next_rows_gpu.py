@@ -174,3 +174,27 @@ def test_renderer_token_major_equals_channel_major():
     assert (d > 1e-3).float().mean().item() <= 1e-4 and d.max().item() <= 1.0 / 255 + 1e-3
     from tests.helpers import psnr
     assert psnr(imgs[0].cpu(), imgs[1].cpu()) > 60
+
+
+def test_token_major_decode_backward_equals_channel_major():
+    """Training in the producer's layout: dL/dtokens (transposed), dL/dW, dL/db, dL/dpoints from the token-major
+    autograd node equal the channel-major node's (itself checked against torch CPU autograd in test_train_gpu.py)."""
+    from audio_motion_avatar_b200.stages import decode_gaussians_autograd, decoder_matrix
+    C, R, F, N = 64, 16, 3, 3000
+    g = torch.Generator().manual_seed(21)
+    tokens = torch.randn(F, C, 3 * R * R, generator=g).cuda()
+    pts = (torch.rand(F, N, 3, generator=g) * 2.4 - 1.2).cuda()
+    transl = torch.randn(F, 3, generator=g).cuda()
+    Wd, bd = decoder_matrix(S.make_decoder_weights(C, seed=3))
+    cot = {k: torch.randn(F, N, n, generator=g).cuda() for k, n in (("xyz", 3), ("scale", 3), ("rot", 4), ("opacity", 1), ("color", 3))}
+    grads = []
+    for tm in (False, True):
+        tk = (tokens.transpose(1, 2).contiguous() if tm else tokens.clone()).requires_grad_(True)
+        p_, t_ = pts.clone().requires_grad_(True), transl.clone().requires_grad_(True)
+        W_, b_ = Wd.cuda().clone().requires_grad_(True), bd.cuda().clone().requires_grad_(True)
+        out = decode_gaussians_autograd(tk, p_, t_, W_, b_, C, R, 1.4, token_major=tm)
+        sum((out[k] * cot[k]).sum() for k in cot).backward()
+        grads.append((tk.grad.transpose(1, 2) if tm else tk.grad, p_.grad, t_.grad, W_.grad, b_.grad))
+    for a, b, name in zip(grads[0], grads[1], ("tokens", "points", "transl", "weight", "bias")):
+        err = (a - b).abs().max().item() / max(a.abs().max().item(), 1e-12)
+        assert err < 1e-4, (name, err)
