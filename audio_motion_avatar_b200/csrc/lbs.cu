@@ -261,25 +261,48 @@ __global__ void __launch_bounds__(256) skin_kernel(int V, int J, const float *__
     o[2] = T2.x * x + T2.y * y + T2.z * z + T2.w;
 }
 
-// sites[f][i] = sum_k wgt[i][k] * verts[f][par[i][k]]
-__global__ void __launch_bounds__(256) densify_kernel(int V, int N, int P, const float *__restrict__ verts,
+// sites[f][i] = sum_k wgt[i][k] * verts[f][par[i][k]].  A thread keeps its site's table row in registers for DEN_FB
+// frames (P == 4, the level-2 table: one int4 + one float4 load); the sums run in the same order as one frame at a time.
+constexpr int DEN_FB = 8;
+
+__global__ void __launch_bounds__(256) densify_kernel(int F, int V, int N, int P, const float *__restrict__ verts,
                                                        const int32_t *__restrict__ par, const float *__restrict__ wgt,
-                                                       float *__restrict__ sites)
+                                                       float *__restrict__ sites, int vec4)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const int f = blockIdx.y;
+    const int f0 = blockIdx.y * DEN_FB, f1 = min(F, f0 + DEN_FB);
     if (i >= N) return;
-    const float *vb = verts + (int64_t)f * V * 3;
-    float x = 0.0f, y = 0.0f, z = 0.0f;
-    for (int k = 0; k < P; ++k) {
-        const float w = __ldg(wgt + (int64_t)i * P + k);
-        if (w != 0.0f) {
-            const int q = __ldg(par + (int64_t)i * P + k);
-            x = fmaf(w, vb[3 * q], x); y = fmaf(w, vb[3 * q + 1], y); z = fmaf(w, vb[3 * q + 2], z);
+    if (vec4) {
+        const int4 q = __ldg(reinterpret_cast<const int4 *>(par) + i);
+        const float4 w = __ldg(reinterpret_cast<const float4 *>(wgt) + i);
+        const int qq[4] = {q.x, q.y, q.z, q.w};
+        const float ww[4] = {w.x, w.y, w.z, w.w};
+        for (int f = f0; f < f1; ++f) {
+            const float *vb = verts + (int64_t)f * V * 3;
+            float x = 0.0f, y = 0.0f, z = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (ww[k] != 0.0f) {
+                    x = fmaf(ww[k], vb[3 * qq[k]], x); y = fmaf(ww[k], vb[3 * qq[k] + 1], y); z = fmaf(ww[k], vb[3 * qq[k] + 2], z);
+                }
+            float *o = sites + ((int64_t)f * N + i) * 3;
+            o[0] = x; o[1] = y; o[2] = z;
         }
+        return;
     }
-    float *o = sites + ((int64_t)f * N + i) * 3;
-    o[0] = x; o[1] = y; o[2] = z;
+    for (int f = f0; f < f1; ++f) {
+        const float *vb = verts + (int64_t)f * V * 3;
+        float x = 0.0f, y = 0.0f, z = 0.0f;
+        for (int k = 0; k < P; ++k) {
+            const float w = __ldg(wgt + (int64_t)i * P + k);
+            if (w != 0.0f) {
+                const int q = __ldg(par + (int64_t)i * P + k);
+                x = fmaf(w, vb[3 * q], x); y = fmaf(w, vb[3 * q + 1], y); z = fmaf(w, vb[3 * q + 2], z);
+            }
+        }
+        float *o = sites + ((int64_t)f * N + i) * 3;
+        o[0] = x; o[1] = y; o[2] = z;
+    }
 }
 
 }  // namespace
@@ -354,8 +377,9 @@ extern "C" int amav_densify_gather(int F, int V, int N, int P, const float *vert
     AMAV_CHECK_ARG(F >= 0 && F <= 65535 && V > 0 && N >= 0 && P >= 1, "bad dims");
     if ((int64_t)F * N == 0) return AMAV_OK;
     AMAV_CHECK_ARG(verts && par && wgt && sites, "null buffer");
-    dim3 g(amav_div_up(N, 256), F);
-    densify_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(V, N, P, verts, par, wgt, sites);
+    dim3 g(amav_div_up(N, 256), amav_div_up(F, DEN_FB));
+    const int vec4 = P == 4 && ((uintptr_t)par & 15) == 0 && ((uintptr_t)wgt & 15) == 0;
+    densify_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(F, V, N, P, verts, par, wgt, sites, vec4);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }
