@@ -114,7 +114,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t *__res
 constexpr int SCAT_CHUNK = 2048;
 constexpr int SCAT_PER = SCAT_CHUNK / 256;
 
-__global__ void __launch_bounds__(256, 4) scatter_entries(int N, int gx, int tiles, const float4 *__restrict__ geom,
+__global__ void __launch_bounds__(256, 3) scatter_entries(int N, int gx, int tiles, const float4 *__restrict__ geom,
                                                         const ushort4 *__restrict__ rect,
                                                         const uint32_t *__restrict__ tile_start,
                                                         uint32_t *__restrict__ tile_cursor,
@@ -139,10 +139,18 @@ __global__ void __launch_bounds__(256, 4) scatter_entries(int N, int gx, int til
     if (use_smem) {
         for (int t = threadIdx.x; t < tiles; t += 256) s_pos[t] = 0u;
         __syncthreads();
+        // one flat loop per rectangle (w * h trips): lanes whose rectangles differ in shape but not in area stay together
 #pragma unroll
-        for (int k = 0; k < SCAT_PER; ++k)
-            for (int y = rc[k].y; y < rc[k].w; ++y)
-                for (int x = rc[k].x; x < rc[k].z; ++x) atomicAdd(&s_pos[y * gx + x], 1u);
+        for (int k = 0; k < SCAT_PER; ++k) {
+            const int w = (int)rc[k].z - (int)rc[k].x, h = (int)rc[k].w - (int)rc[k].y;
+            const int cnt = (w > 0 && h > 0) ? w * h : 0;
+            int t = rc[k].y * gx + rc[k].x, x = 0;
+            for (int e = 0; e < cnt; ++e) {
+                atomicAdd(&s_pos[t], 1u);
+                ++t;
+                if (++x == w) { x = 0; t += gx - w; }
+            }
+        }
         __syncthreads();
         // four tiles per thread and step: the tile_start loads and the cursor atomics of a step are in flight together
         for (int t0 = threadIdx.x; t0 < tiles; t0 += 4 * 256) {
@@ -167,14 +175,16 @@ __global__ void __launch_bounds__(256, 4) scatter_entries(int N, int gx, int til
         if (rc[k].z <= rc[k].x || rc[k].w <= rc[k].y) continue;
         const uint32_t i = (uint32_t)(blockIdx.x * SCAT_CHUNK + k * 256 + threadIdx.x);
         const uint64_t e = ((uint64_t)__float_as_uint(depth[k]) << 32) | (uint64_t)i;
-        for (int y = rc[k].y; y < rc[k].w; ++y)
-            for (int x = rc[k].x; x < rc[k].z; ++x) {
-                const int t = y * gx + x;
-                const int64_t pos = use_smem ? (int64_t)atomicAdd(&s_pos[t], 1u)
-                                             : (int64_t)tile_start[tbase + t] + atomicAdd(tile_cursor + tbase + t, 1u);
-                if (pos < capacity) entries[pos] = e;
-                else *overflow = 1;
-            }
+        const int w = (int)rc[k].z - (int)rc[k].x, cnt = w * ((int)rc[k].w - (int)rc[k].y);
+        int t = rc[k].y * gx + rc[k].x, x = 0;
+        for (int q = 0; q < cnt; ++q) {
+            const int64_t pos = use_smem ? (int64_t)atomicAdd(&s_pos[t], 1u)
+                                         : (int64_t)tile_start[tbase + t] + atomicAdd(tile_cursor + tbase + t, 1u);
+            if (pos < capacity) entries[pos] = e;
+            else *overflow = 1;
+            ++t;
+            if (++x == w) { x = 0; t += gx - w; }
+        }
     }
 }
 

@@ -162,8 +162,15 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessParams 
                     g2 = make_float4(cg, cb, pvz, (float)rad);
                     rc = make_ushort4((unsigned short)minx, (unsigned short)miny, (unsigned short)maxx,
                                       (unsigned short)maxy);
-                    for (int y = miny; y < maxy; ++y)
-                        for (int x = minx; x < maxx; ++x) atomicAdd(cnt + y * p.gx + x, 1u);
+                    {   // one flat loop over the rectangle (lanes diverge on area only, not on shape)
+                        const int w = maxx - minx, n = w * (maxy - miny);
+                        int t = miny * p.gx + minx, x = 0;
+                        for (int e = 0; e < n; ++e) {
+                            atomicAdd(cnt + t, 1u);
+                            ++t;
+                            if (++x == w) { x = 0; t += p.gx - w; }
+                        }
+                    }
                 }
             }
         }
