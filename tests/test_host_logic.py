@@ -1,0 +1,62 @@
+"""Host-side logic of the wrappers that needs no GPU: argument validation, the decoder-head packing of the 6D pose
+entry, and that every product entry refuses CPU tensors instead of falling back (there is no CPU path)."""
+import pytest
+import torch
+
+from audio_motion_avatar_b200 import _lib, stages
+
+
+def test_pose_6d_from_decoder_heads_follows_smplx_joint_order():
+    """SMPLX.forward order: global, 21 body, jaw, leye, reye, 15 left hand, 15 right hand; SMPLXDecoder's hand head holds
+    the left hand first (smplx_decoder.py:114-115)."""
+    Fr = 3
+    root = torch.full((Fr, 6), 1.0)
+    body = torch.arange(21 * 6, dtype=torch.float32).repeat(Fr, 1) + 100
+    hand = torch.arange(30 * 6, dtype=torch.float32).repeat(Fr, 1) + 1000
+    jaw, leye, reye = torch.full((Fr, 6), 2.0), torch.full((Fr, 6), 3.0), torch.full((Fr, 6), 4.0)
+    p = stages.pose_6d_from_decoder_heads(root, body, hand, jaw, leye, reye)
+    assert p.shape == (Fr, 55, 6) and p.is_contiguous()
+    assert torch.equal(p[:, 0], root) and torch.equal(p[:, 1:22].reshape(Fr, -1), body)
+    assert torch.equal(p[:, 22], jaw) and torch.equal(p[:, 23], leye) and torch.equal(p[:, 24], reye)
+    assert torch.equal(p[:, 25:40].reshape(Fr, -1), hand[:, :90]) and torch.equal(p[:, 40:].reshape(Fr, -1), hand[:, 90:])
+
+
+def test_frames_to_u8_validates_arguments_and_refuses_cpu_tensors():
+    fr = torch.rand(2, 8, 8, 3)
+    with pytest.raises(ValueError):
+        stages.frames_to_u8(fr[..., :2])                                  # not 3 channels
+    with pytest.raises(ValueError):
+        stages.frames_to_u8(fr.double())
+    with pytest.raises(ValueError):
+        stages.frames_to_u8(fr, out_first=1)                              # placement needs an explicit buffer
+    with pytest.raises(ValueError):
+        stages.frames_to_u8(fr, out=torch.empty(2, 8, 8, 3, dtype=torch.uint8), out_first=0, out_step=2)   # frame 1 would land at index 2
+    with pytest.raises(ValueError):
+        stages.frames_to_u8(fr, out=torch.empty(2, 8, 8, 3, dtype=torch.float32))
+    with pytest.raises(_lib.AmavError):
+        stages.frames_to_u8(fr)                                           # CPU tensor: no CPU path
+
+
+def test_triplane_project_validates_layout_and_refuses_cpu_tensors():
+    C, R = 64, 16
+    w = torch.zeros(14, 3 + 3 * C)
+    with pytest.raises(ValueError):
+        stages.triplane_project(torch.zeros(1, C, 3 * R * R), w, C, R, token_major=True)   # channel-major given as token-major
+    with pytest.raises(ValueError):
+        stages.triplane_project(torch.zeros(1, 3 * R * R, C), w, C, R)
+    with pytest.raises(_lib.AmavError):
+        stages.triplane_project(torch.zeros(1, 3 * R * R, C), w, C, R, token_major=True)
+    with pytest.raises(_lib.AmavError):
+        stages.triplane_project(torch.zeros(1, C, 3 * R * R), w, C, R)
+
+
+def test_every_header_symbol_has_a_ctypes_signature():
+    import os
+    import re
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "amav.h")).read()
+    declared = set(re.findall(r"\b(amav_[a-z0-9_]+)\s*\(", src))
+    special = {"amav_last_error", "amav_version", "amav_launch_count", "amav_splat_scan_tmp_elems", "amav_splat_scan_order_offset"}
+    assert declared - special == set(_lib._SIGS), (declared - special) ^ set(_lib._SIGS)
+    for name in ("amav_lbs_forward_6d", "amav_lbs_backward_6d", "amav_triplane_project_tm", "amav_triplane_project_backward_tm",
+                 "amav_frames_to_u8"):
+        assert name in declared
