@@ -87,6 +87,33 @@ __device__ __forceinline__ void amav_exp_x2(float x0, float x1, const ExpConsts 
     e1 = __int_as_float(__float_as_int(p1) + ((__float_as_int(r1) - __float_as_int(MAGIC)) << 23));
 }
 
+// Two amav_exp evaluations in ONE instruction stream of sm_100 packed-FP32 operations (fma.rn.f32x2 / add.rn.f32x2:
+// SASS FFMA2 / FADD2, each half IEEE round-to-nearest, so e.x == amav_exp(x.x) and e.y == amav_exp(x.y) bit for bit).
+// The range reduction is written on the NEGATED sum: rn = fma(x, -log2e, -MAGIC) = -r exactly (round-to-nearest is
+// symmetric), so -n = MAGIC - r = rn + MAGIC needs no negated operand (the packed instructions have no negate
+// modifier in PTX), and the exponent insertion only uses the low mantissa bits of r, which -r shares:
+// (bits(r) - bits(MAGIC)) << 23 == bits(rn) << 23 (mod 2^32).  9 packed FP instructions + 2 integer ones per half.
+__device__ __forceinline__ float2 amav_exp_f32x2(const float2 x)
+{
+    const float L2E_HI = 1.44269502162933349609375f;
+    const float L2E_LO = 1.925963033500011e-8f;
+    const float MAGIC = 12582912.0f;
+    const float2 rn = __ffma2_rn(x, make_float2(-L2E_HI, -L2E_HI), make_float2(-MAGIC, -MAGIC));
+    const float2 mn = __fadd2_rn(rn, make_float2(MAGIC, MAGIC));
+    float2 f = __ffma2_rn(x, make_float2(L2E_HI, L2E_HI), mn);
+    f = __ffma2_rn(x, make_float2(L2E_LO, L2E_LO), f);
+    float2 p = __ffma2_rn(make_float2(0.001326472731307149f, 0.001326472731307149f), f,
+                          make_float2(0.009671512991189957f, 0.009671512991189957f));
+    p = __ffma2_rn(p, f, make_float2(0.05550733581185341f, 0.05550733581185341f));
+    p = __ffma2_rn(p, f, make_float2(0.24022242426872253f, 0.24022242426872253f));
+    p = __ffma2_rn(p, f, make_float2(0.6931470036506653f, 0.6931470036506653f));
+    p = __ffma2_rn(p, f, make_float2(1.0f, 1.0f));
+    float2 e;
+    e.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(rn.x) << 23));
+    e.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(rn.y) << 23));
+    return e;
+}
+
 // 16-byte shared-memory load at a 32-bit shared address + immediate offset.  The list walk addresses its records
 // as base + 48 j with the base held in a register; through a generic pointer ptxas rebuilds the shared window
 // base (S2R SR_CgaCtaId + LEA) for every entry.
@@ -133,11 +160,12 @@ constexpr int SUB_W = 8, SUB_H = 4;        // pixels of one warp: 8 wide x 4 tal
 // quadratic optimum.  A Gaussian whose bound is below pmin (minus a rounding margin) cannot reach alpha >= 1/255
 // at any pixel of the rectangle: the exact per-pixel test would reject it 32 times, so dropping it from the
 // warp's list changes nothing in the result.
+template <int RW = SUB_W, int RH = SUB_H>
 __device__ __forceinline__ bool warp_rect_keep(const float4 a, const float4 b, float x0, float y0)
 {
     const float Ah = a.z, Bn = a.w, Ch = b.x, pmin = b.z;
-    const float dxl = a.x - (x0 + (float)(SUB_W - 1)), dxh = a.x - x0;
-    const float dyl = a.y - (y0 + (float)(SUB_H - 1)), dyh = a.y - y0;
+    const float dxl = a.x - (x0 + (float)(RW - 1)), dxh = a.x - x0;
+    const float dyl = a.y - (y0 + (float)(RH - 1)), dyh = a.y - y0;
     if (!(Ah < 0.0f && Ch < 0.0f)) return true;                       // degenerate conic (or NaN): exact path decides
     const bool out_x = dxl > 0.0f || dxh < 0.0f, out_y = dyl > 0.0f || dyh < 0.0f;
     if (!out_x && !out_y) return true;                                // centre inside the rectangle

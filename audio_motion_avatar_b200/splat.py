@@ -61,7 +61,8 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
                   bg: torch.Tensor, height: int, width: int, *, views_per_set: int = 1, activate: bool = False,
                   hwc: bool = False, clamp01: bool = False, want_aux: bool = False, want_invdepth: bool = False,
                   scale_modifier: float = 1.0, workspace: Optional[SplatWorkspace] = None,
-                  sync_free: bool = False, out: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+                  sync_free: bool = False, out: Optional[torch.Tensor] = None,
+                  row_stores: Optional[bool] = None) -> Dict[str, torch.Tensor]:
     """Render F frames.
 
     means3d/scales/colors [G,N,3], rots [G,N,4], opacities [G,N,1] with G = F // views_per_set
@@ -69,6 +70,8 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     bg [3].  Returns a dict with ``color`` ([F,3,H,W], or [F,H,W,3] when ``hwc``) plus the
     intermediate buffers (``geom``, ``rect``, ``tiles_touched``, ``tile_start``, ``point_list``, ``D``
     and, with ``want_aux``, ``final_T`` / ``n_contrib``) used by the backward pass and the parity tests.
+    ``row_stores`` (HWC inference only): None lets the library decide (row stores when ``out`` is another GPU's memory),
+    True / False force the choice (include/amav.h: AMAV_LAYOUT_HWC_ROWS / _PIXELS).
     """
     dev = means3d.device
     if dev.type != "cuda":
@@ -118,7 +121,8 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     final_T = torch.empty(F, height, width, dtype=torch.float32, device=dev) if want_aux else None
     n_contrib = torch.empty(F, height, width, dtype=torch.int32, device=dev) if want_aux else None
     invdepth = torch.empty(F, 1, height, width, dtype=torch.float32, device=dev) if want_invdepth else None
-    call("amav_splat_blend", dims, ptr(geom), ptr(tile_start), ptr(ws.point_list), ws.capacity, ptr(bg), int(hwc), int(clamp01),
+    layout = 0 if not hwc else 1 if row_stores is None else 2 if row_stores else 3
+    call("amav_splat_blend", dims, ptr(geom), ptr(tile_start), ptr(ws.point_list), ws.capacity, ptr(bg), layout, int(clamp01),
          ptr(out), ptr(final_T), ptr(n_contrib), ptr(invdepth), ptr(work_counter), ptr(tile_order), st)
     return {"color": out, "tile_order": tile_order, "geom": geom.view(F, N, 12), "rect": rect.view(F, N, 4), "tiles_touched": touched.view(F, N),
             "tile_start": tile_start, "point_list": ws.point_list, "D": D, "final_T": final_T,

@@ -4,6 +4,10 @@
  *
  * Conventions
  *   - every pointer is a DEVICE pointer unless its name starts with h_;
+ *   - DEVICE CONTRACT: kernels are launched on the calling thread's CURRENT CUDA device (cudaSetDevice) and on
+ *     `stream`, which must belong to that device; every buffer must be memory of that device, with the one documented
+ *     exception of amav_splat_blend's out_color, which may be a peer mapping of another GPU's memory.  The Python
+ *     mirror makes the tensors' device current around every call (audio_motion_avatar_b200/_lib.py: call);
  *   - the caller allocates every input, output and workspace buffer; the library never
  *     allocates, frees or keeps state between calls (except the last-error string);
  *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no call synchronises
@@ -28,6 +32,13 @@ extern "C" {
 #define AMAV_EINVAL (-1)   /* bad argument                           */
 #define AMAV_ECUDA (-2)    /* CUDA launch / runtime error            */
 #define AMAV_ECAP (-3)     /* caller-provided capacity too small     */
+
+/* colour layout argument (`hwc`) of amav_splat_blend / amav_splat_blend_backward */
+#define AMAV_LAYOUT_CHW 0         /* [F,3,H,W]: what GaussianRasterizer returns per frame (renderer.py:557) */
+#define AMAV_LAYOUT_HWC 1         /* [F,H,W,3]: what render_batch returns (renderer.py:477-479); the library asks the driver
+                                     whether out_color is another GPU's memory and then stores whole rows (cached per pointer) */
+#define AMAV_LAYOUT_HWC_ROWS 2    /* HWC, row stores forced (the caller knows the buffer is a peer mapping); forward only */
+#define AMAV_LAYOUT_HWC_PIXELS 3  /* HWC, per-pixel stores forced; forward only */
 
 #define AMAV_TILE 16       /* tile edge in pixels (upstream BLOCK_X/BLOCK_Y) */
 #define AMAV_DEC_OUT 14    /* decoded attributes per Gaussian: xyz3 rot4 scale3 opacity1 shs3 */
@@ -165,7 +176,7 @@ int amav_splat_bin(const AmavSplatDims *d, const float *geom, const uint16_t *re
                    int32_t *point_list, int64_t capacity, int32_t *overflow, void *stream);
 
 /* 4c  blend (upstream renderCUDA) over all tiles of all frames.
- *   bg [3]; out_color [F,3,H,W] (hwc=0) or [F,H,W,3] (hwc=1, the layout render_batch returns,
+ *   bg [3]; out_color [F,3,H,W] (hwc=AMAV_LAYOUT_CHW) or [F,H,W,3] (AMAV_LAYOUT_HWC*, the layout render_batch returns,
  *   renderer.py:477-479); clamp01=1 applies renderer.py:568.
  *   final_T [F,H,W], n_contrib [F,H,W] int32, out_invdepth [F,H,W]: each may be NULL (inference).
  *   capacity: entries in point_list (same value as given to amav_splat_bin); tile ranges are clamped to it.

@@ -29,6 +29,15 @@
  *     <= 1.5 ulp of exp over the range used).  Upstream uses CUDA expf (<= 2 ulp), which
  *     no CPU can reproduce bit for bit; define AMAV_ORACLE_LIBM_EXP to use
  *     libm expf instead (tests check the two agree to ~1e-7 relative).
+ *   - AMAV_ORACLE_UPSTREAM_ARITH (libamav_oracle_upstream.so, `make upstream`): the blend's
+ *     per-pair arithmetic as upstream WRITES it -- libm expf and the literal
+ *     power = -0.5f*(con.x*dx*dx + con.z*dy*dy) - con.y*dx*dy, no FMA -- instead of the
+ *     FMA nesting and polynomial shared with the kernels.  tests/test_oracle_upstream.py and
+ *     bench.py count how many alpha >= 1/255 / T < 1e-4 decisions (n_contrib) and pixels
+ *     differ between the two builds: the distance between "our oracle" and "upstream's
+ *     arithmetic".  Preprocess and binning are identical in both builds.
+ *   - the loops over Gaussians / merge runs carry OpenMP pragmas; every iteration is
+ *     independent, so results do not depend on the thread count.
  */
 #include <math.h>
 #include <stdint.h>
@@ -46,7 +55,7 @@ static inline int imax(int a, int b) { return a > b ? a : b; }
 /* exp(x) for x <= 0 (blend only evaluates it for power <= 0). */
 float amav_oracle_exp(float x)
 {
-#ifdef AMAV_ORACLE_LIBM_EXP
+#if defined(AMAV_ORACLE_LIBM_EXP) || defined(AMAV_ORACLE_UPSTREAM_ARITH)
     return expf(x);
 #else
     if (x < -80.0f) x = -80.0f;
@@ -94,6 +103,9 @@ void amav_oracle_preprocess(
     const float limx = 1.3f * tanfovx;
     const float limy = 1.3f * tanfovy;
 
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
     for (int i = 0; i < N; ++i) {
         radii[i] = 0;
         tiles_touched[i] = 0;
@@ -225,6 +237,9 @@ void amav_oracle_emit_keys(int N, const int32_t *radii, const int32_t *rect,
                            uint64_t *keys, int32_t *values)
 {
     const int gx = (W + BLOCK_X - 1) / BLOCK_X;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
     for (int i = 0; i < N; ++i) {
         if (radii[i] <= 0) continue;
         int64_t off = (i == 0) ? 0 : offsets[i - 1];
@@ -249,6 +264,9 @@ void amav_oracle_sort_pairs(int64_t D, uint64_t *keys, int32_t *values)
     uint64_t *ka = keys, *kb = kt;
     int32_t *va = values, *vb = vt;
     for (int64_t w = 1; w < D; w *= 2) {
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) if (D / (2 * w) >= 4)
+#endif
         for (int64_t lo = 0; lo < D; lo += 2 * w) {
             int64_t mid = lo + w < D ? lo + w : D;
             int64_t hi = lo + 2 * w < D ? lo + 2 * w : D;
@@ -330,7 +348,13 @@ void amav_oracle_blend(int W, int H, const int32_t *ranges, const int32_t *point
                     const float Ch = -0.5f * conic_opacity[4 * g + 2];
                     const float dx = xy[2 * g] - pxf;
                     const float dy = xy[2 * g + 1] - pyf;
+#ifdef AMAV_ORACLE_UPSTREAM_ARITH
+                    (void)Ah; (void)Bn; (void)Ch;
+                    const float power = -0.5f * (conic_opacity[4 * g] * dx * dx + conic_opacity[4 * g + 2] * dy * dy)
+                                        - conic_opacity[4 * g + 1] * dx * dy;
+#else
                     const float power = fmaf(fmaf(Bn, dy, Ah * dx), dx, (Ch * dy) * dy);
+#endif
                     if (power > 0.0f) continue;
                     const float alpha = fminf(0.99f, conic_opacity[4 * g + 3] * amav_oracle_exp(power));
                     if (alpha < alpha_min) continue;

@@ -299,25 +299,65 @@ def activate_for_raster(g: Dict[str, torch.Tensor]) -> Tuple[torch.Tensor, torch
 # ----------------------------------------------------------------------------------------
 # a-9  rasteriser: ctypes binding of oracle/raster_oracle.c
 # ----------------------------------------------------------------------------------------
-_LIB = None
+_LIBS: Dict[str, ctypes.CDLL] = {}
+_VARIANT = "exact"          # which build raster_* calls go to: "exact" | "upstream" | "fast" (see oracle/Makefile)
 
 
-def build_c_oracle(force: bool = False) -> str:
-    so = os.path.join(_HERE, "libamav_oracle.so")
+def _host_tag() -> str:
+    """The fast build is compiled -march=native, so its file name carries a hash of this host's CPU flags: a .so
+    built in the CPU container is not run on a GPU box with another CPU (it is rebuilt there; gcc is in the image)."""
+    import hashlib
+    try:
+        with open("/proc/cpuinfo") as fh:
+            flags = next((ln for ln in fh if ln.startswith("flags")), "")
+    except OSError:
+        flags = ""
+    return hashlib.sha1(flags.encode()).hexdigest()[:10]
+
+
+def build_c_oracle(force: bool = False, variant: str = "exact") -> str:
     src = os.path.join(_HERE, "raster_oracle.c")
+    if variant == "exact":
+        so, target = os.path.join(_HERE, "libamav_oracle.so"), ["libamav_oracle.so"]
+    elif variant == "upstream":
+        so, target = os.path.join(_HERE, "libamav_oracle_upstream.so"), ["libamav_oracle_upstream.so"]
+    elif variant == "fast":
+        name = f"libamav_oracle_fast_{_host_tag()}.so"
+        so, target = os.path.join(_HERE, name), ["fast", f"FAST_OUT={name}"]
+    else:
+        raise ValueError(variant)
     if force or not os.path.exists(so) or (os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(so)):
-        subprocess.check_call(["make", "-s", "-C", _HERE, "libamav_oracle.so"])
+        subprocess.check_call(["make", "-s", "-C", _HERE] + target)
     return so
 
 
-def _lib():
-    global _LIB
-    if _LIB is None:
-        _LIB = ctypes.CDLL(build_c_oracle())
-        _LIB.amav_oracle_scan.restype = ctypes.c_int64
-        _LIB.amav_oracle_exp.restype = ctypes.c_float
-        _LIB.amav_oracle_exp.argtypes = [ctypes.c_float]
-    return _LIB
+def _lib(variant: Optional[str] = None):
+    variant = variant or _VARIANT
+    L = _LIBS.get(variant)
+    if L is None:
+        L = ctypes.CDLL(build_c_oracle(variant=variant))
+        L.amav_oracle_scan.restype = ctypes.c_int64
+        L.amav_oracle_exp.restype = ctypes.c_float
+        L.amav_oracle_exp.argtypes = [ctypes.c_float]
+        _LIBS[variant] = L
+    return L
+
+
+class oracle_variant:
+    """``with oracle_variant("upstream"):`` routes the raster_* calls below to another build of raster_oracle.c."""
+
+    def __init__(self, variant: str):
+        self.variant = variant
+
+    def __enter__(self):
+        global _VARIANT
+        self._prev, _VARIANT = _VARIANT, self.variant
+        _lib(self.variant)
+        return self
+
+    def __exit__(self, *exc):
+        global _VARIANT
+        _VARIANT = self._prev
 
 
 def _p(a: np.ndarray):

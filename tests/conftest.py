@@ -10,6 +10,7 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "slow: tens of seconds of CPU oracle (configs[4] sizes); AMAV_SKIP_SLOW=1 skips them")
 
 
 @pytest.fixture(scope="session")

@@ -53,7 +53,7 @@ def _stage_isolated_images(g, cams, H, W):
     return torch.stack(imgs)
 
 
-def _compare(img, g, ref_img, ref_g, cams):
+def _compare(img, g, ref_img, ref_g, cams, iso_flips_ok=False):
     for k in ("xyz", "scale", "rot", "opacity", "color"):
         err = (g[k].cpu() - ref_g[k]).abs().max().item()
         assert err <= 1e-3, (k, err)
@@ -62,7 +62,14 @@ def _compare(img, g, ref_img, ref_g, cams):
     H, W = a.shape[2], a.shape[3]
     # (1) splat stage in isolation, same Gaussians and cameras on both sides: north_star's image tolerance
     iso = _stage_isolated_images(g, cams, H, W).numpy().reshape(a.shape)
-    assert np.abs(a - iso).max() <= 1e-3, np.abs(a - iso).max()
+    if iso_flips_ok:
+        # megapixel frames: the kernel activates scale / opacity itself (CUDA expf) while this check activates on the CPU, so
+        # ulp-level differences move isolated (pixel, Gaussian) pairs across the alpha >= 1/255 cut (<= ~1/255 per flip).
+        # The bit-exact stage-isolated comparison (identical activated inputs) is tests/test_config_parity_gpu.py's.
+        di = np.abs(a - iso)
+        assert (di > 1e-3).mean() <= 1e-5 and di.max() <= 1.0 / 255.0 + 1e-3, ((di > 1e-3).mean(), di.max())
+    else:
+        assert np.abs(a - iso).max() <= 1e-3, np.abs(a - iso).max()
     assert psnr(a, iso) >= 60.0
     # (2) end to end: the attributes differ by ~1e-5 between the two paths, so a few (pixel, Gaussian) pairs fall on
     # the other side of the rasteriser's alpha >= 1/255 cut; each flip moves a pixel by at most ~1/255.

@@ -168,29 +168,31 @@ def test_equal_depths_fall_back_to_the_sorting_network():
     _check_frame(out, 0, pre, binned, img, N, H, W)
 
 
-@pytest.mark.parametrize("W,H", [(96, 72), (64, 40)])
-def test_row_store_variant_equals_per_pixel_stores(W, H, monkeypatch):
+@pytest.mark.parametrize("W,H", [(96, 72), (64, 40), (1024, 1024)])
+def test_row_store_variant_equals_per_pixel_stores(W, H):
     """The blend instantiation used when the frames are written into another GPU's buffer (tile pairs, colour leaves
     as 16 rows of 384 bytes) produces the same HWC frames as the per-pixel stores, including the rows below the image
-    edge in the last tile row.  AMAV_ROW_STORES=1 forces it on a local buffer (the library otherwise picks it by
-    cudaPointerGetAttributes); W must be a multiple of 32, other widths keep the per-pixel path."""
+    edge in the last tile row.  row_stores=True forces it on a local buffer (AMAV_LAYOUT_HWC_ROWS; the library otherwise
+    picks it by cudaPointerGetAttributes); W must be a multiple of 32, other widths are rejected."""
+    from audio_motion_avatar_b200._lib import AmavError
     from audio_motion_avatar_b200.splat import splat_forward
-    N = 4000
+    N = 4000 if W < 1024 else 60000
     sc = random_scene(N, W, H, seed=21)
     view, full, tan = oracle_cameras(sc, H, W)
     d = torch.device("cuda:0")
     c = lambda t: t.to(d)
 
-    def run():
+    def run(rows, width=W):
         out = splat_forward(c(sc["means"])[None], c(sc["scales"])[None], c(sc["rots"])[None], c(sc["opac"])[None],
-                            c(sc["col"])[None], c(view), c(full), c(tan), torch.tensor([0.2, 0.5, 0.9], device=d), H, W,
-                            views_per_set=view.shape[0], hwc=True, clamp01=True)["color"].clone()
+                            c(sc["col"])[None], c(view), c(full), c(tan), torch.tensor([0.2, 0.5, 0.9], device=d), H, width,
+                            views_per_set=view.shape[0], hwc=True, clamp01=True, row_stores=rows)["color"].clone()
         torch.cuda.synchronize()
         return out
 
-    monkeypatch.delenv("AMAV_ROW_STORES", raising=False)
-    ref = run()
-    monkeypatch.setenv("AMAV_ROW_STORES", "1")
-    rows = run()
-    assert ref.shape == (view.shape[0], H, W, 3) and torch.equal(ref, rows)
+    ref = run(False)
+    rows = run(True)
+    auto = run(None)                                   # a local buffer: the library keeps the per-pixel stores
+    assert ref.shape == (view.shape[0], H, W, 3) and torch.equal(ref, rows) and torch.equal(ref, auto)
     assert (ref != torch.tensor([0.2, 0.5, 0.9], device=d)).any()          # something was actually rendered
+    with pytest.raises(AmavError):
+        run(True, width=W + 8)
