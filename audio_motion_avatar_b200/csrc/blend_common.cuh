@@ -130,6 +130,13 @@ template <int OFF> __device__ __forceinline__ float2 lds64(uint32_t addr)
     return v;
 }
 
+template <int OFF> __device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u16 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+    return v;
+}
+
 // Tile queue of the blend kernels.  A tile is one CTA's sequential walk and list lengths differ by orders of
 // magnitude, so a deep tile handed out late leaves the whole GPU waiting for one CTA (a 4-frame training launch
 // lasts exactly as long as its deepest tile).  amav_splat_scan lists the deep tiles (`order`: [0] = number with

@@ -39,7 +39,9 @@ struct BlendParams {
     uint32_t capacity;
 };
 
-template <bool DEPTH, bool ROWS>
+// AUX: final_T / n_contrib / inverse depth are wanted (training, parity tests); the inference instantiations do not
+// track the last contributor at all.
+template <bool AUX, bool ROWS>
 __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams p, const float *__restrict__ bg)
 {
     // one 48-byte record per staged entry: (x, y, -conic.x/2, -conic.y)(-conic.z/2, opacity, pmin, r)(g, b, depth, radius);
@@ -148,35 +150,40 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
                 const float2 oma = __ffma2_rn(alpha, make_float2(-1.0f, -1.0f), make_float2(1.0f, 1.0f));   // 1 - alpha
                 const float2 Tn = __fmul2_rn(T, oma);
                 float2 w = __fmul2_rn(alpha, T);
-                const bool low0 = Tn.x < 0.0001f, low1 = Tn.y < 0.0001f;
-                const bool live0 = ok0 && !low0, live1 = ok1 && !low1;
+                const bool live0 = ok0 && !(Tn.x < 0.0001f), live1 = ok1 && !(Tn.y < 0.0001f);
                 w.x = live0 ? w.x : 0.0f;
                 w.y = live1 ? w.y : 0.0f;
                 const float2 c = lds64<32>(rec);
                 C0 = __ffma2_rn(make_float2(b.w, b.w), w, C0);
                 C1 = __ffma2_rn(make_float2(c.x, c.x), w, C1);
                 C2 = __ffma2_rn(make_float2(c.y, c.y), w, C2);
-                if (DEPTH) {
+                if (AUX && p.out_invdepth) {
                     const float inv = 1.0f / lds64<40>(rec).x;
                     Dv = __ffma2_rn(make_float2(inv, inv), w, Dv);
                 }
-                T.x = live0 ? Tn.x : T.x;
-                T.y = live1 ? Tn.y : T.y;
-                if (ok0 && low0) T.x = -fabsf(T.x);                     // saturated: upstream's done = true
-                if (ok1 && low1) T.y = -fabsf(T.y);
-                if (live0) off0_last = (int)rec;
-                if (live1) off1_last = (int)rec;
+                // an accepted pair either advances T or saturates the pixel (upstream's done = true): one guarded select
+                if (ok0) T.x = live0 ? Tn.x : -fabsf(T.x);
+                if (ok1) T.y = live1 ? Tn.y : -fabsf(T.y);
+                if (AUX) {
+                    if (live0) off0_last = (int)rec;
+                    if (live1) off1_last = (int)rec;
+                }
             };
             int k = 0;
-            for (; k + 1 < cnt; k += 2) {
-                uint32_t both;                                           // two 16-bit list entries in one load
-                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(both) : "r"(list_base + 2u * (uint32_t)k));
-                blend_entry(both & 0xffffu);
-                blend_entry(both >> 16);
+#pragma unroll 1
+            for (; k + 3 < cnt; k += 4) {
+                const uint32_t la = list_base + 2u * (uint32_t)k;
+                blend_entry(lds_u16<0>(la));
+                blend_entry(lds_u16<2>(la));
+                blend_entry(lds_u16<4>(la));
+                blend_entry(lds_u16<6>(la));
             }
-            if (k < cnt) blend_entry(list[k]);
-            if (off0_last >= 0) last0 = before + (off0_last - (int)rec_base) / 48 + 1;
-            if (off1_last >= 0) last1 = before + (off1_last - (int)rec_base) / 48 + 1;
+#pragma unroll 1
+            for (; k < cnt; ++k) blend_entry(lds_u16<0>(list_base + 2u * (uint32_t)k));
+            if (AUX) {
+                if (off0_last >= 0) last0 = before + (off0_last - (int)rec_base) / 48 + 1;
+                if (off1_last >= 0) last1 = before + (off1_last - (int)rec_base) / 48 + 1;
+            }
         }
         // colour epilogue.  ROWS: HWC tile pairs go through shared memory and leave as 16 rows of 384 contiguous bytes
         const int64_t hw = (int64_t)p.H * p.W;
@@ -203,9 +210,11 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
                         o[0] = o0; o[hw] = o1; o[2 * hw] = o2;
                     }
                 }
-                if (p.final_T) p.final_T[(int64_t)f * hw + pix] = Tf;
-                if (p.n_contrib) p.n_contrib[(int64_t)f * hw + pix] = h ? last1 : last0;
-                if (DEPTH) p.out_invdepth[(int64_t)f * hw + pix] = h ? Dv.y : Dv.x;
+                if (AUX) {
+                    if (p.final_T) p.final_T[(int64_t)f * hw + pix] = Tf;
+                    if (p.n_contrib) p.n_contrib[(int64_t)f * hw + pix] = h ? last1 : last0;
+                    if (p.out_invdepth) p.out_invdepth[(int64_t)f * hw + pix] = h ? Dv.y : Dv.x;
+                }
             }
             if (ROWS) {                              // stage this tile's colour: 96 floats per row of the pair
                 float *so = s_out + (ly + 4 * h) * 96 + half * 48 + lx * 3;
@@ -281,7 +290,7 @@ extern "C" int amav_splat_blend(const AmavSplatDims *d, const float *geom, const
     p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity;
     const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;
     const int grid = (int)(total_tiles < AMAV_SM_COUNT * 8 ? total_tiles : AMAV_SM_COUNT * 8);
-    if (out_invdepth) blend_kernel<true, false><<<grid, FWD_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
+    if (out_invdepth || final_T || n_contrib) blend_kernel<true, false><<<grid, FWD_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
     else if (rows) blend_kernel<false, true><<<grid, FWD_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
     else blend_kernel<false, false><<<grid, FWD_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
     AMAV_CHECK_LAUNCH();
