@@ -5,6 +5,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import threading
 from ctypes import c_double, c_float, c_int, c_int32, c_int64, c_void_p
 
 import torch
@@ -74,19 +75,38 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
-def ptr(t):
-    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+_tls = threading.local()
+
+
+def ptr(t, peer: bool = False):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL); ``peer``: the buffer may be another GPU's memory
+    mapped into this process (amav_splat_blend's out_color) and does not take part in the device check.  The tensor's device is remembered until the next
+    ``call``: the C ABI launches on the calling thread's CURRENT device (include/amav.h, device contract), so ``call``
+    makes the arguments' device current and refuses arguments that live on different devices."""
     if t is None:
         return None
     if not t.is_cuda:
         raise AmavError("libamav_b200 takes CUDA tensors only (no CPU path)")
     if not t.is_contiguous():
         raise AmavError("tensor must be contiguous")
+    if not peer:
+        devs = getattr(_tls, "devs", None)
+        if devs is None:
+            devs = _tls.devs = set()
+        devs.add(t.device.index)
     return c_void_p(t.data_ptr())
 
 
+class _StreamOfArguments:
+    """Placeholder for the `stream` argument: ``call`` replaces it by the current stream of the device the pointer
+    arguments live on (not of whatever device happens to be current)."""
+
+
+_STREAM = _StreamOfArguments()
+
+
 def stream_ptr():
-    return c_void_p(torch.cuda.current_stream().cuda_stream)
+    return _STREAM
 
 
 class StageTimer:
@@ -125,6 +145,22 @@ def call(name: str, *args) -> None:
     fn = getattr(lib(), name, None)
     if fn is None:
         raise AmavError(f"{name} is not exported by {LIB_PATH}")
+    devs = getattr(_tls, "devs", None)
+    _tls.devs = set()
+    if devs and len(devs) > 1:
+        raise AmavError(f"{name}: arguments live on different CUDA devices {sorted(devs)}; every buffer of a call must "
+                        "belong to one device (include/amav.h, device contract)")
+    cur = torch.cuda.current_device()
+    idx = next(iter(devs)) if devs else cur
+    st = c_void_p(torch.cuda.current_stream(idx).cuda_stream)
+    args = [st if a is _STREAM else a for a in args]
+    if idx != cur:
+        with torch.cuda.device(idx):
+            return _call_on_current_device(name, fn, args)
+    return _call_on_current_device(name, fn, args)
+
+
+def _call_on_current_device(name, fn, args) -> None:
     if _TIMER is not None:
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()

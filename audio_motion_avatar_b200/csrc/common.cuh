@@ -20,6 +20,8 @@
 
 void amav_set_error(const char *fmt, ...);
 void amav_count_launches(int n);
+// opt-in to `bytes` of dynamic shared memory for `func` on the current device, once (capi.cu)
+cudaError_t amav_ensure_dyn_smem(const void *func, int bytes);
 
 #define AMAV_CHECK_ARG(cond, msg)                                   \
     do {                                                            \

@@ -339,7 +339,7 @@ static int lbs_forward_impl(bool sixd, int F, int V, int J, int S, const float *
         lbs_pose_kernel<false><<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, pose_feature, joints, A);
     const size_t smem = (size_t)(K + S) * PB_F * sizeof(float);
     AMAV_CHECK_ARG(smem <= 200 * 1024, "pose basis too large");
-    cudaFuncSetAttribute(pose_blend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    amav_ensure_dyn_smem((const void *)pose_blend_kernel, (int)smem);
     dim3 gb(amav_div_up(V, PB_THREADS), amav_div_up(F, PB_F));
     pose_blend_kernel<<<gb, PB_THREADS, smem, stream>>>(F, V, S, K, pose_feature, shape_comp, v_template, shapedirs,
                                                         posedirs, v_posed);

@@ -373,7 +373,7 @@ static int lbs_backward_impl(bool sixd, int F, int V, int J, int S, const float 
     skin_bwd_kernel<<<gs, 256, 0, stream>>>(V, J, weights_T, A, v_posed, d_verts, d_v_posed, d_A);
     const size_t smem = (size_t)(K + S) * PBB_F * sizeof(float);
     AMAV_CHECK_ARG(smem <= 200 * 1024, "pose basis too large");
-    cudaFuncSetAttribute(pose_blend_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    amav_ensure_dyn_smem((const void *)pose_blend_bwd_kernel, (int)smem);
     dim3 gb(amav_div_up(V, PBB_THREADS), amav_div_up(F, PBB_F));
     const int ksplit = (4 * AMAV_SM_COUNT + (int)(gb.x * gb.y) - 1) / (int)(gb.x * gb.y);
     gb.z = ksplit < 1 ? 1 : (ksplit > 8 ? 8 : ksplit);

@@ -510,7 +510,7 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
     AMAV_CHECK_ARG(d->frames <= 65535, "too many frames for one call");
     const size_t hist = (size_t)tiles * sizeof(uint32_t);
     const int use_smem = hist <= 160 * 1024;
-    if (use_smem) cudaFuncSetAttribute(scatter_entries, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist);
+    if (use_smem) amav_ensure_dyn_smem((const void *)scatter_entries, (int)hist);
     dim3 sgrid(amav_div_up(d->num_gaussians, SCAT_CHUNK), d->frames);
     scatter_entries<<<sgrid, 256, use_smem ? hist : 0, stream>>>(
         d->num_gaussians, gx, tiles, reinterpret_cast<const float4 *>(geom), reinterpret_cast<const ushort4 *>(rect),
@@ -522,8 +522,8 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
     const int64_t want = (nt + SORT_SMALL_POP - 1) / SORT_SMALL_POP;
     const int grid = (int)(want < AMAV_SM_COUNT * 4 ? want : AMAV_SM_COUNT * 4);
     const int small_smem = SORT_SMALL_CAP * 12, large_smem = SORT_LARGE_CAP * 12;
-    cudaFuncSetAttribute(small, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);
-    cudaFuncSetAttribute(large, cudaFuncAttributeMaxDynamicSharedMemorySize, large_smem);
+    amav_ensure_dyn_smem((const void *)small, small_smem);
+    amav_ensure_dyn_smem((const void *)large, large_smem);
     small<<<grid, SORT_SMALL_T, small_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
                                                       reinterpret_cast<unsigned int *>(overflow) + 1);
     AMAV_CHECK_LAUNCH();

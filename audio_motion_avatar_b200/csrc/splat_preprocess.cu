@@ -214,7 +214,7 @@ extern "C" int amav_splat_preprocess(const AmavSplatDims *d, const float *means3
     AMAV_CHECK_ARG(d->frames <= 65535, "too many frames for one call");
     const size_t hist = (size_t)p.gx * p.gy * sizeof(uint32_t);
     const int use_smem = hist <= 160 * 1024;
-    if (use_smem) cudaFuncSetAttribute(preprocess_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist);
+    if (use_smem) amav_ensure_dyn_smem((const void *)preprocess_kernel, (int)hist);
     dim3 grid(amav_div_up(d->num_gaussians, PRE_CHUNK), d->frames);
     preprocess_kernel<<<grid, 256, use_smem ? hist : 0, (cudaStream_t)stream>>>(p, use_smem);
     AMAV_CHECK_LAUNCH();

@@ -211,7 +211,7 @@ extern "C" int amav_triplane_project(int F, int C, int R, const float *tokens, i
     AMAV_CHECK_ARG(((uintptr_t)tokens & 15) == 0 && (token_frame_stride & 3) == 0, "tokens must be 16-byte aligned");
     const size_t smem = ((size_t)C * 16 + (size_t)PJ_KGROUPS * 14 * PJ_TEX) * sizeof(float);
     AMAV_CHECK_ARG(smem <= 113 * 1024, "C too large for the shared-memory weight tile");
-    cudaFuncSetAttribute(project_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    amav_ensure_dyn_smem((const void *)project_kernel, (int)smem);
     const int64_t grid = (int64_t)F * 3 * (R * R / PJ_TEX);
     AMAV_CHECK_ARG(grid < ((int64_t)1 << 31), "too many tiles");
     project_kernel<<<(unsigned)grid, PJ_THREADS, smem, (cudaStream_t)stream>>>(C, R * R, tokens, token_frame_stride,

@@ -355,7 +355,7 @@ extern "C" int amav_triplane_project_backward(int F, int C, int R, const float *
                        ((uintptr_t)d_tokens & 15) == 0, "bad d_tokens stride / alignment");
         const size_t smem = (size_t)C * 16 * sizeof(float);
         AMAV_CHECK_ARG(smem <= 100 * 1024, "C too large for the shared-memory weight tile");
-        cudaFuncSetAttribute(project_bwd_tokens_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        amav_ensure_dyn_smem((const void *)project_bwd_tokens_kernel, (int)smem);
         project_bwd_tokens_kernel<<<(unsigned)grid, PB_THREADS_T, smem, stream>>>(C, R * R, d_proj, weight, 3 + 3 * C, d_tokens,
                                                                                  d_token_frame_stride, accumulate_tokens);
         AMAV_CHECK_LAUNCH();

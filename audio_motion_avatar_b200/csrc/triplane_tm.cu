@@ -256,7 +256,7 @@ extern "C" int amav_triplane_project_tm(int F, int C, int R, const float *tokens
     const size_t tile_floats = (size_t)TM_STAGES * TM_TILE, red_floats = (size_t)TM_WARPS * 14 * TM_TEX;
     const size_t smem = ((size_t)C * 16 + (tile_floats > red_floats ? tile_floats : red_floats)) * sizeof(float);
     AMAV_CHECK_ARG(smem <= 200 * 1024, "C too large for the shared-memory weight tile");
-    cudaFuncSetAttribute(project_tm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    amav_ensure_dyn_smem((const void *)project_tm_kernel, (int)smem);
     const int64_t grid = (int64_t)F * 3 * (R * R / TM_TEX);
     AMAV_CHECK_ARG(grid < ((int64_t)1 << 31), "too many tiles");
     project_tm_kernel<<<(unsigned)grid, TM_THREADS, smem, (cudaStream_t)stream>>>(C, R * R, tokens_tm, token_frame_stride,

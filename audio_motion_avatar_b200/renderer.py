@@ -75,14 +75,18 @@ def _background(bg_color, device) -> torch.Tensor:
     return t
 
 
-_WORKSPACES: Dict[int, SplatWorkspace] = {}
+_WORKSPACES: Dict[tuple, SplatWorkspace] = {}
 
 
 def _workspace(device) -> SplatWorkspace:
+    """The inference workspace (bucket buffers, tile counters, overflow flag) of the CURRENT STREAM of ``device``: calls
+    enqueued on one stream are ordered and can share it; two streams (or a CUDA-graph capture, which runs on its own
+    stream) render concurrently and get their own buffers.  The C ABI itself is re-entrant."""
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    ws = _WORKSPACES.get(idx)
+    key = (idx, torch.cuda.current_stream(idx).cuda_stream)
+    ws = _WORKSPACES.get(key)
     if ws is None:
-        ws = _WORKSPACES[idx] = SplatWorkspace()
+        ws = _WORKSPACES[key] = SplatWorkspace()
     return ws
 
 
@@ -230,6 +234,77 @@ class _Decoder(nn.Module):
     pass
 
 
+class GraphedForward:
+    """``Renderer.forward`` (inference) captured in a CUDA graph for fixed shapes.
+
+    The tensors given to the constructor ARE the graph's static inputs (``copy_inputs=False``: zero-copy, the producer
+    refills them in place before ``replay()``) or are cloned (``copy_inputs=True``); ``__call__`` copies any tensor that
+    is not the static one into it first.  ``images`` / ``gaussians`` are the static outputs (overwritten by the next
+    replay).  Bucket capacity is fixed from a sizing run; the overflow flag is read by ``overflowed()`` (one host sync)
+    and ``recapture()`` re-sizes, exactly as the eager path's deferred checks."""
+
+    def __init__(self, renderer, tokens, cams, params, out=None, copy_inputs: bool = False, warmup: int = 2):
+        dev = renderer._device
+        own = (lambda t: t.to(dev).clone()) if copy_inputs else (lambda t: t if t.device == dev else t.to(dev))
+        self.renderer = renderer
+        self.tokens = own(tokens)
+        self.cams = {k: own(v) for k, v in cams.items()}
+        self.params = {k: own(v) for k, v in params.items()}
+        self.out = out
+        self.warmup = warmup
+        self.stream = torch.cuda.Stream(dev)
+        self.graph = None
+        self._capture()
+
+    def _capture(self):
+        r, dev = self.renderer, self.renderer._device
+        if _lib._TIMER is not None:
+            raise _lib.AmavError("StageTimer records timing events, which a stream capture does not allow")
+        self.stream.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(self.stream), torch.no_grad():
+            for _ in range(max(1, self.warmup)):         # sizes this stream's workspace (the one read of D) and warms up
+                r(self.tokens, self.cams, None, self.params, out=self.out)
+            self.stream.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            n0 = _lib.launch_count()
+            with deferred_overflow_checks() as chk:
+                with torch.cuda.graph(self.graph, stream=self.stream):
+                    res = r(self.tokens, self.cams, None, self.params, out=self.out)
+            self.launches = _lib.launch_count() - n0     # library kernels inside one replay
+            self._chk = chk
+        self.images, self.gaussians = res[0], res[1]
+        torch.cuda.current_stream(dev).wait_stream(self.stream)
+
+    def replay(self):
+        self.graph.replay()
+        return self.images, self.gaussians
+
+    def overflowed(self) -> bool:
+        return self._chk.overflowed()
+
+    def recapture(self):
+        """After an overflow: drop the cached capacity of the capture stream's workspace and capture again."""
+        dev = self.renderer._device
+        with torch.cuda.stream(self.stream):
+            _workspace(dev).capacity = 0
+        self._capture()
+
+    def __call__(self, tokens=None, cams=None, params=None, check: bool = True):
+        def put(dst, src):
+            if src is not None and src.data_ptr() != dst.data_ptr():
+                dst.copy_(src, non_blocking=True)
+        put(self.tokens, tokens)
+        for k, v in (cams or {}).items():
+            put(self.cams[k], v)
+        for k, v in (params or {}).items():
+            put(self.params[k], v)
+        self.replay()
+        if check and self.overflowed():
+            self.recapture()
+            self.replay()
+        return self.images, self.gaussians
+
+
 class Renderer(nn.Module):
     """renderer.py:20-346.  ``Renderer(cfg, smpl_decoder=None, body_model=None)``; ``body_model`` (a buffer dict as
     from ``synthetic.make_body_model`` / ``load_smplx_model``) replaces ``cfg.smplx_model_path`` when no SMPL-X
@@ -296,6 +371,9 @@ class Renderer(nn.Module):
         n = int(self._dense_par.shape[0])
         g = None if seed is None else torch.Generator().manual_seed(seed)
         self._fixed_idx = torch.randperm(n, generator=g)[:self.num_verts].to(self._device)
+        # the subset's rows of the densify table, gathered once instead of on every forward
+        self._fixed_par = self._dense_par.index_select(0, self._fixed_idx).contiguous()
+        self._fixed_wgt = self._dense_wgt.index_select(0, self._fixed_idx).contiguous()
         return self._fixed_idx
 
     def get_smpl_vertices(self, smpl_params):
@@ -313,11 +391,16 @@ class Renderer(nn.Module):
             full, shape = self.smplx_model.full_pose(smpl_params)
             verts = stages.lbs_vertices(self.smplx_model, full, shape)
         if getattr(self.cfg, "densify_smplx_verts", False):
-            idx = self._fixed_idx
-            if idx is None:
+            if self._fixed_idx is not None:
+                par, wgt = self._fixed_par, self._fixed_wgt
+            else:
+                if torch.cuda.is_current_stream_capturing():
+                    raise _lib.AmavError("a CUDA-graph capture cannot redraw torch.randperm on the CPU generator "
+                                         "(renderer.py:287): call fix_site_subset() first")
                 idx = torch.randperm(int(self._dense_par.shape[0]))[:self.num_verts].to(self._device)
-            verts = stages.densify_sites(verts, self._dense_par.index_select(0, idx).contiguous(),
-                                         self._dense_wgt.index_select(0, idx).contiguous())
+                par = self._dense_par.index_select(0, idx).contiguous()
+                wgt = self._dense_wgt.index_select(0, idx).contiguous()
+            verts = stages.densify_sites(verts, par, wgt)
         return verts
 
     def _decoder_wb(self):
@@ -409,6 +492,13 @@ class Renderer(nn.Module):
         if getattr(self.cfg, "predict_smplx_params", False):
             return rendered, gaussians, pred_smpl_params
         return rendered, gaussians
+
+    def capture(self, triplane_features, cam_params, smpl_params, out=None, copy_inputs: bool = False):
+        """CUDA-graph the inference forward for these shapes: returns a ``GraphedForward`` whose ``replay()`` re-runs the
+        whole path (LBS -> densify -> project -> sample/decode -> camera -> preprocess -> scan -> bin -> blend) as ONE
+        graph launch -- no per-kernel launch cost, no host work, no host sync.  The reference hands the renderer T = 6
+        frames per call (configs/model/triplane_audio_net.yaml:4): at that size the eager call is launch-bound."""
+        return GraphedForward(self, triplane_features, cam_params, smpl_params, out=out, copy_inputs=copy_inputs)
 
     # -- host-resident sequences ------------------------------------------------------------------
     def render_sequence(self, triplane_features, cam_params, smpl_params, chunk: int = 8, out=None,

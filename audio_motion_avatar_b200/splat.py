@@ -123,7 +123,7 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
     invdepth = torch.empty(F, 1, height, width, dtype=torch.float32, device=dev) if want_invdepth else None
     layout = 0 if not hwc else 1 if row_stores is None else 2 if row_stores else 3
     call("amav_splat_blend", dims, ptr(geom), ptr(tile_start), ptr(ws.point_list), ws.capacity, ptr(bg), layout, int(clamp01),
-         ptr(out), ptr(final_T), ptr(n_contrib), ptr(invdepth), ptr(work_counter), ptr(tile_order), st)
+         ptr(out, peer=True), ptr(final_T), ptr(n_contrib), ptr(invdepth), ptr(work_counter), ptr(tile_order), st)
     return {"color": out, "tile_order": tile_order, "geom": geom.view(F, N, 12), "rect": rect.view(F, N, 4), "tiles_touched": touched.view(F, N),
             "tile_start": tile_start, "point_list": ws.point_list, "D": D, "final_T": final_T,
             "n_contrib": n_contrib, "invdepth": invdepth, "workspace": ws}

@@ -211,3 +211,98 @@ def test_diff_gaussian_rasterization_shim_runs_reference_render_one():
     for k in raw:
         ga, gb = a[k].grad, b[k].grad
         assert (ga - gb).abs().max().item() <= 1e-3 * gb.abs().max().item() + 1e-7, k
+
+
+def _small_renderer(H=160, W=128, C=64, R=16, N=20000):
+    from audio_motion_avatar_b200.renderer import Renderer
+    r = Renderer(make_cfg(H, W, C, R, densify=True, steps=2, num_gaussians=N), body_model=S.make_body_model(seed=0))
+    r.gaussian_decoder.load_state_dict(S.make_decoder_weights(C, seed=1))
+    r.fix_site_subset(0)
+    return r
+
+
+def _inputs(T, H, W, C, R, seed):
+    cu = lambda d: {k: v.cuda() for k, v in d.items()}
+    return S.make_triplane_tokens(T, C, R, seed=seed).cuda(), cu(S.make_cameras(1, T, H, W)), cu(S.make_pose_sequence(1, T, seed=seed))
+
+
+def test_cuda_graph_replay_equals_eager_bit_for_bit():
+    """Renderer.capture: the whole inference forward as one CUDA graph at the reference's native clip length (T = 6,
+    triplane_audio_net.yaml:4).  Replay == eager bit for bit, also after the static inputs are refilled in place and when
+    other tensors are handed to __call__; an overflow of the captured bucket capacity is seen and repaired by recapture."""
+    H, W, C, R, T = 160, 128, 64, 16, 6
+    r = _small_renderer(H, W, C, R)
+    tok, cams, par = _inputs(T, H, W, C, R, seed=1)
+    tok2, cams2, par2 = _inputs(T, H, W, C, R, seed=2)
+    with torch.no_grad():
+        img, g = r(tok, cams, None, par)
+        img_b, g_b = r(tok2, cams2, None, par2)
+    gf = r.capture(tok, cams, par, copy_inputs=True)
+    assert 10 <= gf.launches <= 20                           # the library's kernels of one forward, all inside the graph
+    a, ga = gf.replay()
+    assert torch.equal(a, img) and all(torch.equal(ga[k], g[k]) for k in g)
+    gf.tokens.copy_(tok2)                                    # producer writes the static buffers in place
+    for k in par2:
+        gf.params[k].copy_(par2[k])
+    b, gb = gf.replay()
+    assert torch.equal(b, img_b) and all(torch.equal(gb[k], g_b[k]) for k in g_b) and not gf.overflowed()
+    c, _ = gf(tok, cams, par)                                # other tensors: copied into the static inputs first
+    assert torch.equal(c, img)
+    # overflow: a graph captured with the body behind the camera (no tile entries at all) replayed with the body in view
+    far = {k: v.clone() for k, v in par.items()}
+    far["transl"][..., 2] = -5.0
+    gf2 = r.capture(tok, cams, far, copy_inputs=True)
+    gf2.replay()
+    assert not gf2.overflowed()
+    for k in par:
+        gf2.params[k].copy_(par[k])
+    gf2.replay()
+    assert gf2.overflowed()                                  # frames incomplete, nothing read out of bounds
+    d, _ = gf2(check=True)                                   # recapture with the sizing read, then replay
+    assert torch.equal(d, img) and not gf2.overflowed()
+
+
+def test_two_streams_render_concurrently_with_their_own_workspaces():
+    """The Python mirror keeps one splat workspace per (device, stream): two streams rendering different sequences at
+    the same time must not share tile cursors, overflow flags or bucket buffers."""
+    H, W, C, R, T = 160, 128, 64, 16, 4
+    r = _small_renderer(H, W, C, R)
+    ins = [_inputs(T, H, W, C, R, seed=s) for s in (3, 4)]
+    with torch.no_grad():
+        ref = [r(t, c, None, p)[0].clone() for t, c, p in ins]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [None, None]
+    for rep in range(3):
+        for i, st in enumerate(streams):
+            with torch.cuda.stream(st), torch.no_grad():
+                outs[i] = r(*ins[i][:2], None, ins[i][2])[0]
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], ref[0]) and torch.equal(outs[1], ref[1])
+
+
+def test_call_runs_on_the_tensors_device_not_the_current_one():
+    """kernels must launch on the device that owns the tensors.  With a second GPU the renderer lives on
+    cuda:1 while cuda:0 stays current; with one GPU the contract is checked through the mixed-device error."""
+    from audio_motion_avatar_b200 import _lib
+    if torch.cuda.device_count() < 2:
+        a = torch.zeros(4, device="cuda:0")
+        _lib.ptr(a)
+        _lib._tls.devs.add(7)                                # as if a second argument lived on another device
+        with pytest.raises(_lib.AmavError):
+            _lib.call("amav_camera_setup", 0, None, None, 1, 1, 0.01, 100.0, None, None, None, _lib.stream_ptr())
+        return
+    from audio_motion_avatar_b200.renderer import Renderer
+    H, W, C, R = 96, 80, 64, 16
+    cfg0, cfg1 = make_cfg(H, W, C, R), make_cfg(H, W, C, R)
+    cfg1.device = "cuda:1"
+    model, wts = S.make_body_model(seed=0), S.make_decoder_weights(C, seed=0)
+    r0, r1 = Renderer(cfg0, body_model=model), Renderer(cfg1, body_model=model)
+    r0.gaussian_decoder.load_state_dict(wts); r1.gaussian_decoder.load_state_dict(wts)
+    tok, cams, par = S.make_triplane_tokens(2, C, R, seed=0), S.make_cameras(1, 2, H, W), S.make_pose_sequence(1, 2, seed=0)
+    to = lambda d, dev: {k: v.to(dev) for k, v in d.items()}
+    torch.cuda.set_device(0)
+    with torch.no_grad():
+        a = r0(tok.to("cuda:0"), to(cams, "cuda:0"), None, to(par, "cuda:0"))[0]
+        b = r1(tok.to("cuda:1"), to(cams, "cuda:1"), None, to(par, "cuda:1"))[0]
+    assert torch.cuda.current_device() == 0 and b.device.index == 1 and torch.equal(a.cpu(), b.cpu())
