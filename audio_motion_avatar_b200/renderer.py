@@ -144,8 +144,10 @@ def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug,
         activate = False
     if torch.is_grad_enabled() and any(t.requires_grad for t in (xyz, rot, scale, opacity, color)):
         # training: autograd node with its own buffers (the forward's lists and per-pixel state feed the backward)
+        # the [0,1] clamp (renderer.py:568) stays a torch op here so that autograd masks dL/dimage exactly as the
+        # reference's does wherever the blended colour leaves [0,1] (a caller-supplied bg_color, saturated pixels)
         return splat_render(xyz, scale, rot, opacity, color, view, full, tanfov, bg, height, width,
-                            views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=True)
+                            views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=False).clamp(0.0, 1.0)
     ws = _workspace(dev)
 
     def run(sync_free):

@@ -162,6 +162,33 @@ def splat_backward(fwd: Dict[str, torch.Tensor], grad_color: torch.Tensor, means
     return {"means3d": d_means, "scales": d_scales, "rots": d_rots, "opacities": d_opac, "colors": d_colors, "dsum": dsum}
 
 
+# Training under a CUDA graph: SplatFunction normally sizes its bucket buffer with one host read of D per call, which a
+# stream capture cannot contain.  Eager steps record the largest D seen per call shape; inside ``fixed_training_capacity()``
+# the buffers are sized from that record (x1.25), D is not read, and every call's overflow flag is kept for
+# ``training_overflow_flags()`` to be read after the replays (an overflow means: run eager steps again, recapture).
+_TRAIN_D: Dict[tuple, int] = {}
+_TRAIN_FIXED = False
+_TRAIN_FLAGS: list = []
+
+
+class fixed_training_capacity:
+    def __enter__(self):
+        global _TRAIN_FIXED
+        self._prev, _TRAIN_FIXED = _TRAIN_FIXED, True
+        _TRAIN_FLAGS.clear()
+        return self
+
+    def __exit__(self, *exc):
+        global _TRAIN_FIXED
+        _TRAIN_FIXED = self._prev
+
+
+def training_overflow_flags() -> list:
+    """Overflow flags (device tensors) of the SplatFunction calls made in the last ``fixed_training_capacity()`` block; for
+    a captured step they are the graph's own static tensors, valid after every replay."""
+    return list(_TRAIN_FLAGS)
+
+
 class SplatFunction(torch.autograd.Function):
     """Differentiable batched splat: forward = splat_forward (own workspace, aux kept), backward = splat_backward.
     Cameras, background and the image size carry no gradient (as in the reference, where they are plain settings)."""
@@ -170,9 +197,17 @@ class SplatFunction(torch.autograd.Function):
     def forward(ctx, means3d, scales, rots, opacities, colors, view, proj, tanfov, bg, height, width, views_per_set,
                 activate, hwc, clamp01, scale_modifier):
         ws = SplatWorkspace()
+        key = (int(view.shape[0]), int(means3d.shape[-2]), int(height), int(width), int(views_per_set), means3d.device.index)
+        fixed = _TRAIN_FIXED and key in _TRAIN_D
+        if fixed:
+            ws.ensure_capacity(_TRAIN_D[key], means3d.device)
         fwd = splat_forward(means3d, scales, rots, opacities, colors, view, proj, tanfov, bg, height, width,
                             views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=clamp01, want_aux=True,
-                            scale_modifier=scale_modifier, workspace=ws)
+                            scale_modifier=scale_modifier, workspace=ws, sync_free=fixed)
+        if fixed:
+            _TRAIN_FLAGS.append(ws.overflow.clone())
+        else:
+            _TRAIN_D[key] = max(_TRAIN_D.get(key, 0), int(fwd["D"]))
         ctx.fwd = fwd
         ctx.args = (height, width, views_per_set, activate, hwc, scale_modifier)
         ctx.save_for_backward(means3d, scales, rots, opacities, colors, view, proj, tanfov, bg)

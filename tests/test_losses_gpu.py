@@ -29,7 +29,6 @@ def test_losses_match_reference_golden():
     g, ref = img.grad.cpu().numpy(), d["grad"]
     assert g.shape == ref.shape
     assert np.abs(g - ref).max() <= 1e-4 * np.abs(ref).max()
-    assert not g[0, 0, :6, :7][np.abs(ref[0, 0, :6, :7]) == 0].any() or True
 
 
 @pytest.mark.parametrize("F,H,W", [(3, 70, 45), (2, 128, 160), (1, 16, 16)])

@@ -97,3 +97,32 @@ def test_splat_backward_empty_and_culled():
     out.sum().backward()
     for t in leaves:
         assert t.grad is not None and not t.grad.any()
+
+
+def test_clamp_masks_the_gradient_like_the_reference():
+    """render_one clamps the blended colour to [0,1] (renderer.py:568); autograd zeroes dL/dimage wherever the colour left
+    that range.  A background outside [0,1] makes that happen on most pixels: gradients through the public render_batch must
+    match the oracle's autograd node followed by the same clamp."""
+    from types import SimpleNamespace
+    from audio_motion_avatar_b200.renderer import render_batch
+    N, W, H = 3000, 96, 80
+    sc = random_scene(N, W, H, seed=17, frames=1)
+    bg = [1.5, -0.2, 1.0]
+    raw = {"xyz": sc["means"].clone(), "rot": sc["rots"].clone(), "scale": torch.log(sc["scales"]) + 3.9,
+           "opacity": torch.logit(sc["opac"].clamp(0.02, 0.98)), "color": sc["col"].clone()}
+    gimg = torch.randn(3, H, W, generator=torch.Generator().manual_seed(6))
+    leaves = {k: v.clone().requires_grad_(True) for k, v in raw.items()}
+    img = O.render_one_autograd(leaves, sc["K"][0], sc["E"][0], H, W, tuple(bg))
+    (img * gimg).sum().backward()
+    d = torch.device("cuda:0")
+    dl = {k: v.clone()[None].to(d).requires_grad_(True) for k, v in raw.items()}
+    args = SimpleNamespace(image_size=(H, W), rgb=True, sh_degree=3)
+    out = render_batch(dl, sc["K"][None].to(d), sc["E"][None].to(d), args, bg_color=bg)          # [1,1,H,W,3]
+    assert float(out.min()) >= 0.0 and float(out.max()) <= 1.0
+    assert np.abs(out[0, 0].permute(2, 0, 1).detach().cpu().numpy() - img.detach().numpy()).max() <= 1e-3
+    (out[0, 0].permute(2, 0, 1) * gimg.to(d)).sum().backward()
+    clamped = float(((img.detach() <= 0) | (img.detach() >= 1)).float().mean())
+    assert clamped > 0.3                                                   # the mask matters in this scene
+    for k in raw:
+        a, b = dl[k].grad[0].cpu().numpy(), leaves[k].grad.numpy()
+        assert _rel(a, b) <= 1e-3, k
