@@ -155,7 +155,7 @@ def _render_frames(xyz, rot, scale, opacity, color, K, E, args, bg_color, debug,
                              views_per_set=views_per_set, activate=activate, hwc=hwc, clamp01=True,
                              workspace=ws, sync_free=sync_free, out=out)
 
-    res = run(sync_free=ws.capacity > 0)
+    res = run(sync_free=ws.covers((int(xyz.shape[-2]), height, width, views_per_set), int(view.shape[0])))
     if res["D"] < 0 and not defer_check and _DEFERRED is not None:
         _DEFERRED.append(ws.overflow.clone())           # the flag buffer is reused (zeroed) by the next call
     elif res["D"] < 0 and not defer_check:

@@ -33,6 +33,13 @@ class SplatWorkspace:
     bufs: Dict[str, torch.Tensor] = field(default_factory=dict)
     overflow: Optional[torch.Tensor] = None
     last_D: int = -1
+    # entries per frame seen at the last sizing read, per (N, H, W, views_per_set): a call of another shape (or with
+    # more frames than the cached capacity covers) must not trust the capacity a different workload left behind
+    per_frame: Dict[tuple, float] = field(default_factory=dict)
+
+    def covers(self, key: tuple, frames: int) -> bool:
+        est = self.per_frame.get(key)
+        return est is not None and self.capacity > 0 and self.capacity >= est * frames * 1.1
 
     def get(self, name: str, numel: int, dtype, device, zero: bool = False) -> torch.Tensor:
         t = self.bufs.get(name)
@@ -110,6 +117,7 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
         D = int(tile_start[nt].item()) & 0xFFFFFFFF
         ws.ensure_capacity(D, dev)
         ws.last_D = D
+        ws.per_frame[(N, height, width, views_per_set)] = D / max(F, 1)
     call("amav_splat_bin", dims, ptr(geom), ptr(rect), ptr(tile_start), ptr(tile_cursor), ptr(ws.entries),
          ptr(ws.point_list), ws.capacity, ptr(overflow), st)
 

@@ -122,7 +122,7 @@ def test_clamp_masks_the_gradient_like_the_reference():
     assert np.abs(out[0, 0].permute(2, 0, 1).detach().cpu().numpy() - img.detach().numpy()).max() <= 1e-3
     (out[0, 0].permute(2, 0, 1) * gimg.to(d)).sum().backward()
     clamped = float(((img.detach() <= 0) | (img.detach() >= 1)).float().mean())
-    assert clamped > 0.3                                                   # the mask matters in this scene
+    assert clamped > 0.2                                                   # the mask matters in this scene
     for k in raw:
         a, b = dl[k].grad[0].cpu().numpy(), leaves[k].grad.numpy()
         assert _rel(a, b) <= 1e-3, k
