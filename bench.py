@@ -561,7 +561,7 @@ def train_block(ctx, args, steps=3, warmup=3, size=512, clocks=True, graph=True)
         return loss
 
     ms, clk, launches = ctx.timed(step, steps, warmup, clocks=clocks)
-    loss = step()
+    loss_value = float(step().item())          # (no reference to the loss tensor is kept: it would pin this step's autograd graph)
     with _lib.StageTimer() as timer:
         step()
     stages = {k: {"ms": round(v[0], 4), "calls": v[1]} for k, v in timer.summary().items()}
@@ -574,12 +574,14 @@ def train_block(ctx, args, steps=3, warmup=3, size=512, clocks=True, graph=True)
                       "jobs_total": total_jobs, "jobs_this_rank": my_jobs, "rank0_subjects": subj, "rank0_views": views,
                       "parallelism": ("1 GPU" if world == 1 else f"(subject, view) jobs split over {world} ranks + NCCL all-reduce of "
                                       "dL/dtokens (100 MB) and decoder gradients inside the timed step")},
-           "clocks": clk, "gpu_launches": int(launches), "loss": float(loss.item()), "stages": stages,
+           "clocks": clk, "gpu_launches": int(launches), "loss": loss_value, "stages": stages,
            "library_kernel_ms": round(kernel_ms, 4), "step_over_library_kernel_time": round(ms / kernel_ms, 3) if kernel_ms else None}
     if graph and world == 1:
         try:
             blk["graph"] = train_graph(ctx, step, steps, kernel_ms)
         except Exception as exc:                                     # a capture failure must not cost the eager numbers
+            import traceback
+            traceback.print_exc(file=sys.stderr)
             blk["graph"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
     del r
     return blk
