@@ -301,8 +301,9 @@ class Ctx:
         torch.cuda.set_device(self.local)
         self.dev = torch.device("cuda", self.local)
         if self.world > 1:
-            # NCCL_DEBUG is left as the caller set it: NCCL logs to stdout, and the JSON line is printed LAST, after
-            # the process group is destroyed
+            # NCCL_DEBUG is left as the caller set it.  NCCL logs to stdout by default and keeps logging until the library
+            # unloads (after Python's last line), so its log goes to stderr: stdout then ends with the JSON line
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
             dist.init_process_group("nccl", device_id=self.dev)
 
     def barrier(self):

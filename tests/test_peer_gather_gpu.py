@@ -37,14 +37,28 @@ def _worker(rank, world, port, q):
         tk, cm, pr = shard_inputs(tokens, cams, params, rank, world)
         peer = PeerFrameGather(T, H, W, dev, dst=0)
         out = peer.render(r, tk, cm, pr)
+        ok = True
+        if rank == 0:
+            torch.cuda.synchronize()
+            ok = out is not None and out.shape == (T, H, W, 3) and torch.equal(out, full[0])
         out2 = render_and_gather(r, tk, cm, pr, T, chunks=2, dst=0)
         torch.cuda.synchronize()
         if rank == 0:
-            ok = out is not None and out.shape == (T, H, W, 3) and torch.equal(out, full[0])
             ok = ok and out2 is not None and torch.equal(out2, full[0])
+        # the same shard step as one CUDA graph with the peer stores inside (PeerFrameGather.capture)
+        if rank == 0:
+            peer.local.zero_()
+        dist.barrier()
+        gf = peer.capture(r, tk, cm, pr)
+        for _ in range(2):
+            out3 = peer.render_captured()
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            ok = ok and out3 is not None and torch.equal(out3, full[0]) and gf.launches > 0 and not gf.overflowed()
             q.put(bool(ok))
         else:
-            assert out is None and out2 is None
+            assert out is None and out2 is None and out3 is None
         dist.barrier()
     finally:
         dist.destroy_process_group()
