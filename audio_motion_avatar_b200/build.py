@@ -22,6 +22,7 @@ SOURCES = [
     ("triplane.cu", []),
     ("triplane_bwd.cu", []),
     ("triplane_tm.cu", []),
+    ("triplane_tc.cu", []),
     ("lbs.cu", []),
     ("lbs_bwd.cu", []),
     ("image_loss.cu", []),

@@ -196,11 +196,15 @@ def decoder_matrix(decoder) -> Tuple[torch.Tensor, torch.Tensor]:
     return torch.cat(w, dim=0), torch.cat(b, dim=0)
 
 
+PROJECT_IMPL = "ffma"      # "ffma": FP32 FMA kernel (csrc/triplane.cu); "tc": tcgen05 3xTF32 kernel (csrc/triplane_tc.cu)
+
+
 def triplane_project(tokens: torch.Tensor, weight: torch.Tensor, C: int, R: int,
-                     out: Optional[torch.Tensor] = None, token_major: bool = False) -> torch.Tensor:
+                     out: Optional[torch.Tensor] = None, token_major: bool = False, impl: Optional[str] = None) -> torch.Tensor:
     """tokens [F, C, 3*R*R] (channel-major, renderer.py:85-91; the frame stride may exceed C*3*R*R)
     -> projected planes [F, 3, R*R, 16].  ``token_major``: tokens [F, 3*R*R, C], the layout the upstream
-    transformer computes in before its permute+contiguous (transformers.py:1070-1073)."""
+    transformer computes in before its permute+contiguous (transformers.py:1070-1073).
+    ``impl``: "ffma" or "tc" (tensor cores: tcgen05.mma kind::tf32, 3xTF32 split, accumulator in TMEM); default PROJECT_IMPL."""
     if token_major:
         if tokens.dim() != 3 or tokens.shape[1] != 3 * R * R or tokens.shape[2] != C:
             raise ValueError(f"token-major tokens must be [F,{3 * R * R},{C}], got {tuple(tokens.shape)}")
@@ -224,6 +228,12 @@ def triplane_project(tokens: torch.Tensor, weight: torch.Tensor, C: int, R: int,
     fstride = int(tokens.stride(0)) if Fr > 1 else C * 3 * R * R
     if out is None:
         out = torch.empty(Fr, 3, R * R, 16, device=tokens.device)
+    if (impl or PROJECT_IMPL) == "tc":
+        if C % 32 != 0:
+            raise ValueError("the tensor-core projection needs C % 32 == 0")
+        scratch = torch.empty(3 * (C // 32) * 1024, device=tokens.device)
+        call("amav_triplane_project_tc", Fr, C, R, ctypes_ptr(tokens), fstride, ptr(_f32c(weight)), ptr(scratch), ptr(out), stream_ptr())
+        return out
     call("amav_triplane_project", Fr, C, R, ctypes_ptr(tokens), fstride, ptr(_f32c(weight)), ptr(out), stream_ptr())
     return out
 

@@ -63,6 +63,14 @@ int64_t amav_launch_count(void);
 int amav_triplane_project(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
                           const float *weight, float *proj, void *stream);
 
+/* amav_triplane_project on the 5th-generation tensor cores (csrc/triplane_tc.cu): same inputs and output as
+ * amav_triplane_project; tcgen05.mma kind::tf32 with the fp32 operands split into TF32 hi + lo parts (3 MMAs per K step,
+ * fp32-level accuracy), accumulator in TMEM.  Replaces the five nn.Linear of src/models/renderer.py:165-171 (cuBLAS SGEMM
+ * there).  wprep_scratch: amav_triplane_project_tc_scratch_elems(C) floats of caller-owned scratch (the split weights). */
+int64_t amav_triplane_project_tc_scratch_elems(int C);
+int amav_triplane_project_tc(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
+                             const float *weight, float *wprep_scratch, float *proj, void *stream);
+
 /* Same projection from the producer's own layout: tokens_tm [F, 3*R*R, C] token-major, i.e. the upstream
  * transformer's hidden_states before its `.permute(0, 2, 1).contiguous()` (src/models/transformers.py:1070-1073; the
  * residual it adds afterwards is added in the same layout).  Texel (p, t) of frame f is the C contiguous floats at

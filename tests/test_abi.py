@@ -32,7 +32,7 @@ def test_library_exports_every_declared_symbol():
 def test_ctypes_signatures_cover_the_header():
     from audio_motion_avatar_b200 import _lib
     bound = set(_lib._SIGS) | {"amav_last_error", "amav_version", "amav_launch_count", "amav_splat_scan_tmp_elems",
-             "amav_splat_scan_order_offset"}
+             "amav_splat_scan_order_offset", "amav_triplane_project_tc_scratch_elems"}
     assert set(declared_symbols()) <= bound, set(declared_symbols()) - bound
 
 

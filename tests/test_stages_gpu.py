@@ -120,3 +120,34 @@ def test_project_padded_frame_stride_and_empty():
     assert e.shape[0] == 0
     out = sample_decode(a, torch.zeros(3, 0, 3).cuda(), torch.zeros(3, 3).cuda(), W, torch.zeros(14).cuda(), C, R, 1.4)
     assert out["xyz"].shape == (3, 0, 3)
+
+
+@pytest.mark.parametrize("C,R,F", [(512, 64, 3), (64, 16, 2), (128, 32, 1)])
+def test_tensor_core_projection_matches_float64_and_ffma(C, R, F):
+    """amav_triplane_project_tc (tcgen05.mma kind::tf32, 3xTF32 split, TMEM accumulator) vs float64 W_feat . tokens and
+    vs the FP32-FMA kernel: fp32-level accuracy (<= 2e-5 here; single-pass TF32 would be ~1e-3)."""
+    from audio_motion_avatar_b200 import stages, synthetic as S
+    g = torch.Generator().manual_seed(C + R)
+    tokens = torch.randn(F, C, 3 * R * R, generator=g)
+    W = torch.cat([v for k, v in S.make_decoder_weights(C, seed=3).items() if k.endswith("weight")], 0)     # [14, 3+3C]
+    names = ("xyz", "rotation", "scaling", "opacity", "shs")
+    wd = S.make_decoder_weights(C, seed=3)
+    W = torch.cat([wd[f"{n}_layer.weight"] for n in names], 0)
+    tok_d, W_d = tokens.cuda(), W.cuda()
+    a = stages.triplane_project(tok_d, W_d, C, R, impl="tc")
+    b = stages.triplane_project(tok_d, W_d, C, R, impl="ffma")
+    torch.cuda.synchronize()
+    slot_row = [3, 4, 5, 6, 0, 1, 2, 10, 7, 8, 9, -1, 11, 12, 13, -1]
+    ref = torch.zeros(F, 3, R * R, 16, dtype=torch.float64)
+    for p in range(3):
+        Wp = W[:, 3 + p * C:3 + (p + 1) * C].double()                      # [14, C]
+        T = tokens[:, :, p * R * R:(p + 1) * R * R].double()              # [F, C, R2]
+        out = torch.einsum("oc,fct->fto", Wp, T)                          # [F, R2, 14]
+        for s_, row in enumerate(slot_row):
+            if row >= 0:
+                ref[:, p, :, s_] = out[:, :, row]
+    assert a.shape == b.shape == (F, 3, R * R, 16)
+    err_tc, err_ffma = (a.cpu().double() - ref).abs().max().item(), (b.cpu().double() - ref).abs().max().item()
+    assert err_tc <= 2e-5, err_tc
+    assert err_ffma <= 2e-6, err_ffma           # (the tensor core accumulates with truncation: ~1e-5, the FMA kernel ~3e-7)
+    assert float(a[..., 11].abs().max()) == 0.0 and float(a[..., 15].abs().max()) == 0.0
