@@ -27,12 +27,12 @@ _SIGS = {
     "amav_triplane_project": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
     "amav_triplane_project_tc": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p],
     "amav_triplane_project_tm": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
-    "amav_sample_decode": [c_int, c_int, c_int, c_int, c_float] + [c_void_p] * 10 + [c_void_p],
+    "amav_sample_decode": [c_int, c_int, c_int, c_int, c_float] + [c_void_p] * 11 + [c_void_p],
     "amav_lbs_precompute": [c_int, c_int, c_int] + [c_void_p] * 7 + [c_void_p],
     "amav_lbs_forward": [c_int, c_int, c_int, c_int] + [c_void_p] * 14 + [c_void_p],
     "amav_lbs_forward_6d": [c_int, c_int, c_int, c_int] + [c_void_p] * 14 + [c_void_p],
     "amav_frames_to_u8": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int, c_void_p],
-    "amav_densify_gather": [c_int, c_int, c_int, c_int] + [c_void_p] * 4 + [c_void_p],
+    "amav_densify_gather": [c_int, c_int, c_int, c_int] + [c_void_p] * 5 + [c_void_p],
     "amav_splat_preprocess": [ctypes.POINTER(SplatDims)] + [c_void_p] * 12 + [c_void_p],
     "amav_splat_scan": [ctypes.POINTER(SplatDims)] + [c_void_p] * 3 + [c_void_p],
     "amav_splat_bin": [ctypes.POINTER(SplatDims)] + [c_void_p] * 6 + [c_int64, c_void_p, c_void_p],

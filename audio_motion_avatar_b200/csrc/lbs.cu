@@ -267,11 +267,13 @@ constexpr int DEN_FB = 8;
 
 __global__ void __launch_bounds__(256) densify_kernel(int F, int V, int N, int P, const float *__restrict__ verts,
                                                        const int32_t *__restrict__ par, const float *__restrict__ wgt,
-                                                       float *__restrict__ sites, int vec4)
+                                                       float *__restrict__ sites, int vec4,
+                                                       const int32_t *__restrict__ order)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     const int f0 = blockIdx.y * DEN_FB, f1 = min(F, f0 + DEN_FB);
-    if (i >= N) return;
+    if (slot >= N) return;
+    const int i = order ? __ldg(order + slot) : slot;        // locality order: neighbouring lanes share parent vertices
     if (vec4) {
         const int4 q = __ldg(reinterpret_cast<const int4 *>(par) + i);
         const float4 w = __ldg(reinterpret_cast<const float4 *>(wgt) + i);
@@ -372,14 +374,14 @@ extern "C" int amav_lbs_forward_6d(int F, int V, int J, int S, const float *pose
 }
 
 extern "C" int amav_densify_gather(int F, int V, int N, int P, const float *verts, const int32_t *par,
-                                   const float *wgt, float *sites, void *stream)
+                                   const float *wgt, float *sites, const int32_t *order, void *stream)
 {
     AMAV_CHECK_ARG(F >= 0 && F <= 65535 && V > 0 && N >= 0 && P >= 1, "bad dims");
     if ((int64_t)F * N == 0) return AMAV_OK;
     AMAV_CHECK_ARG(verts && par && wgt && sites, "null buffer");
     dim3 g(amav_div_up(N, 256), amav_div_up(F, DEN_FB));
     const int vec4 = P == 4 && ((uintptr_t)par & 15) == 0 && ((uintptr_t)wgt & 15) == 0;
-    densify_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(F, V, N, P, verts, par, wgt, sites, vec4);
+    densify_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(F, V, N, P, verts, par, wgt, sites, vec4, order);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }

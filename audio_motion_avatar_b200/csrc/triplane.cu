@@ -110,6 +110,7 @@ struct SampleParams {
     const float *weight, *bias;   // decoder [14,3+3C], [14]
     int ldw;
     float *xyz, *scale, *rot, *opacity, *color;
+    const int32_t *order;     // processing order of the sites (a locality order fixed at set-up), or NULL
 };
 
 
@@ -135,9 +136,12 @@ __global__ void __launch_bounds__(256) sample_decode_kernel(const SampleParams p
     __syncthreads();
     // grid = (site groups, frames): no 64-bit division to find the frame
     const int f = blockIdx.y;
-    const int site = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 2);
+    const int slot = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 2);
     const int lane4 = (int)(threadIdx.x & 3);
-    if (site >= p.N) return;
+    if (slot >= p.N) return;
+    // neighbouring thread groups take sites that are neighbours in space (not in the reference's randperm order), so
+    // their taps share texels in L1; every result is written at the site's own index
+    const int site = p.order ? __ldg(p.order + slot) : slot;
     const int64_t gid = (int64_t)f * p.N + site;
     const float px = p.points[3 * gid], py = p.points[3 * gid + 1], pz = p.points[3 * gid + 2];
     const float gx = fminf(fmaxf(px / p.radius, -1.0f), 1.0f);
@@ -222,7 +226,7 @@ extern "C" int amav_triplane_project(int F, int C, int R, const float *tokens, i
 
 extern "C" int amav_sample_decode(int F, int N, int C, int R, float radius, const float *proj, const float *points,
                                   const float *transl, const float *weight, const float *bias, float *xyz,
-                                  float *scale, float *rot, float *opacity, float *color, void *stream_)
+                                  float *scale, float *rot, float *opacity, float *color, const int32_t *order, void *stream_)
 {
     AMAV_CHECK_ARG(F >= 0 && N >= 0 && C > 0 && R > 0 && radius > 0.0f, "bad dims");
     if ((int64_t)F * N == 0) return AMAV_OK;
@@ -233,7 +237,7 @@ extern "C" int amav_sample_decode(int F, int N, int C, int R, float radius, cons
     p.F = F; p.N = N; p.R = R; p.radius = radius;
     p.proj = reinterpret_cast<const float4 *>(proj); p.points = points; p.transl = transl;
     p.weight = weight; p.bias = bias; p.ldw = 3 + 3 * C;
-    p.xyz = xyz; p.scale = scale; p.rot = rot; p.opacity = opacity; p.color = color;
+    p.xyz = xyz; p.scale = scale; p.rot = rot; p.opacity = opacity; p.color = color; p.order = order;
     AMAV_CHECK_ARG(F <= 65535 && (int64_t)3 * R * R * 4 < ((int64_t)1 << 31), "too many frames / planes too large for one call");
     sample_decode_kernel<<<dim3(amav_div_up((int64_t)N * 4, 256), F), 256, 0, stream>>>(p);
     AMAV_CHECK_LAUNCH();

@@ -355,6 +355,13 @@ class Renderer(nn.Module):
             dec.opacity_layer.bias.fill_(inverse_sigmoid(0.1))
         self.gaussian_decoder = dec.to(dev)
         self._fixed_idx = None
+        # processing order of the per-site kernels (stages.locality_order); known whenever the site set is fixed.  Opt-in
+        # (cfg.site_locality_order): measured on B200 at 100k sites x 120 frames it LOSES -- sample_decode 0.92 -> 1.10 ms,
+        # densify 0.20 -> 0.22 ms -- the scattered 12..16-byte result stores and point loads cost more than the shared
+        # texels save
+        self._site_order = None
+        if not getattr(cfg, "densify_smplx_verts", False):
+            self._site_order = stages.locality_order(self.smplx_model.v_template, float(cfg.radius))
 
     # -- densify table (renderer.py:227-243) ------------------------------------------------------
     def init_smplx_subdivider(self, subdivide_steps=2):
@@ -376,6 +383,8 @@ class Renderer(nn.Module):
         # the subset's rows of the densify table, gathered once instead of on every forward
         self._fixed_par = self._dense_par.index_select(0, self._fixed_idx).contiguous()
         self._fixed_wgt = self._dense_wgt.index_select(0, self._fixed_idx).contiguous()
+        rest = stages.densify_gather(self.smplx_model.v_template[None].contiguous(), self._fixed_par, self._fixed_wgt)[0]
+        self._site_order = stages.locality_order(rest, float(self.cfg.radius))
         return self._fixed_idx
 
     def get_smpl_vertices(self, smpl_params):
@@ -393,8 +402,10 @@ class Renderer(nn.Module):
             full, shape = self.smplx_model.full_pose(smpl_params)
             verts = stages.lbs_vertices(self.smplx_model, full, shape)
         if getattr(self.cfg, "densify_smplx_verts", False):
+            order = None
             if self._fixed_idx is not None:
                 par, wgt = self._fixed_par, self._fixed_wgt
+                order = self._site_order if getattr(self.cfg, "site_locality_order", False) else None
             else:
                 if torch.cuda.is_current_stream_capturing():
                     raise _lib.AmavError("a CUDA-graph capture cannot redraw torch.randperm on the CPU generator "
@@ -402,7 +413,7 @@ class Renderer(nn.Module):
                 idx = torch.randperm(int(self._dense_par.shape[0]))[:self.num_verts].to(self._device)
                 par = self._dense_par.index_select(0, idx).contiguous()
                 wgt = self._dense_wgt.index_select(0, idx).contiguous()
-            verts = stages.densify_sites(verts, par, wgt)
+            verts = stages.densify_sites(verts, par, wgt, order)
         return verts
 
     def _decoder_wb(self):
@@ -452,9 +463,16 @@ class Renderer(nn.Module):
         tm = bool(getattr(self.cfg, "triplane_token_major", False))
         if torch.is_grad_enabled() and any(t.requires_grad for t in (triplane_features, points, transl, W, b)):
             return stages.decode_gaussians_autograd(triplane_features, points, transl, W, b, C, R, float(self.cfg.radius),
-                                                    token_major=tm)
+                                                    token_major=tm, order=self._order_for(points))
         proj = stages.triplane_project(triplane_features, W, C, R, token_major=tm)
-        return stages.sample_decode(proj, points, transl, W, b, C, R, float(self.cfg.radius))
+        return stages.sample_decode(proj, points, transl, W, b, C, R, float(self.cfg.radius), order=self._order_for(points))
+
+    def _order_for(self, points):
+        """The locality order applies to the renderer's own site set (densified + fixed subset, or the base vertices)."""
+        o = self._site_order if getattr(self.cfg, "site_locality_order", False) else None
+        if o is None or (getattr(self.cfg, "densify_smplx_verts", False) and self._fixed_idx is None):
+            return None
+        return o if int(points.shape[-2]) == int(o.shape[0]) else None
 
     def forward(self, triplane_features, cam_params, smpl_tokens=None, smpl_params_gt=None, out=None):
         """renderer.py:73-204.  triplane_features [B,T,C,3*R*R]; cam_params {'intrinsic' [B,T,3,3], 'extrinsic'
@@ -564,7 +582,8 @@ class Renderer(nn.Module):
             consumed = torch.cuda.Event()
             consumed.record(main)
             st["tok_free"][slot] = consumed
-            g = stages.sample_decode(proj, points[f0:f1], transl[f0:f1], Wd, bd, C, R, float(self.cfg.radius))
+            g = stages.sample_decode(proj, points[f0:f1], transl[f0:f1], Wd, bd, C, R, float(self.cfg.radius),
+                                     order=self._order_for(points))
             img = st["img"][slot][:n]
             _render_frames(g["xyz"], g["rot"], g["scale"], g["opacity"], g["color"], None, None, self.cfg,
                            bg, False, 1, True, out=img, defer_check=True,

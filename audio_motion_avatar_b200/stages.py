@@ -173,13 +173,13 @@ def frames_to_u8(frames: torch.Tensor, bgr: bool = False, out: Optional[torch.Te
     return out
 
 
-def densify_gather(verts: torch.Tensor, par: torch.Tensor, wgt: torch.Tensor) -> torch.Tensor:
+def densify_gather(verts: torch.Tensor, par: torch.Tensor, wgt: torch.Tensor, order: Optional[torch.Tensor] = None) -> torch.Tensor:
     """sites[f,i] = sum_k wgt[i,k] * verts[f, par[i,k]] (flattened SubdivideMeshes levels + subset,
     renderer.py:276-288).  par int32 [N,P], wgt fp32 [N,P]."""
     Fr, V = int(verts.shape[0]), int(verts.shape[1])
     N, P = int(par.shape[0]), int(par.shape[1])
     sites = torch.empty(Fr, N, 3, device=verts.device)
-    call("amav_densify_gather", Fr, V, N, P, ptr(_f32c(verts)), ptr(par), ptr(wgt), ptr(sites), stream_ptr())
+    call("amav_densify_gather", Fr, V, N, P, ptr(_f32c(verts)), ptr(par), ptr(wgt), ptr(sites), ptr(order), stream_ptr())
     return sites
 
 
@@ -245,7 +245,7 @@ def ctypes_ptr(t: torch.Tensor):
 
 
 def sample_decode(proj: torch.Tensor, points: torch.Tensor, transl: torch.Tensor, weight: torch.Tensor,
-                  bias: torch.Tensor, C: int, R: int, radius: float) -> Dict[str, torch.Tensor]:
+                  bias: torch.Tensor, C: int, R: int, radius: float, order: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
     """Bilinear query of the projected planes at ``points`` [F,N,3] + xyz/bias terms + construct_gaussians
     (renderer.py:292-346).  Returns the reference's ``gaussians`` dict (each [F,N,k]; shs is color)."""
     Fr, N = int(points.shape[0]), int(points.shape[1])
@@ -257,7 +257,7 @@ def sample_decode(proj: torch.Tensor, points: torch.Tensor, transl: torch.Tensor
     color = torch.empty(Fr, N, 3, device=dev)
     call("amav_sample_decode", Fr, N, C, R, float(radius), ptr(proj), ptr(_f32c(points)),
          ptr(_f32c(transl.reshape(Fr, 3))), ptr(_f32c(weight)), ptr(_f32c(bias)), ptr(xyz), ptr(scale), ptr(rot),
-         ptr(opacity), ptr(color), stream_ptr())
+         ptr(opacity), ptr(color), ptr(order), stream_ptr())
     return {"xyz": xyz, "scale": scale, "rot": rot, "opacity": opacity, "color": color, "shs": color}
 
 
@@ -307,9 +307,9 @@ class DecodeFunction(torch.autograd.Function):
     project-then-sample forward, and its hand-written backward (no [F,N,1536] feature tensor in either direction)."""
 
     @staticmethod
-    def forward(ctx, tokens, points, transl, weight, bias, C, R, radius, token_major=False):
+    def forward(ctx, tokens, points, transl, weight, bias, C, R, radius, token_major=False, order=None):
         proj = triplane_project(tokens, weight.detach(), C, R, token_major=token_major)
-        g = sample_decode(proj, points, transl, weight.detach(), bias.detach(), C, R, radius)
+        g = sample_decode(proj, points, transl, weight.detach(), bias.detach(), C, R, radius, order=order)
         ctx.save_for_backward(tokens, points, weight, bias, proj)
         ctx.dims = (C, R, radius)
         ctx.token_major = bool(token_major)
@@ -332,13 +332,13 @@ class DecodeFunction(torch.autograd.Function):
             if d_tokens is not None and d_tokens.shape != tokens.shape:
                 d_tokens = d_tokens.reshape(tokens.shape)
         return (d_tokens, d_points, d_transl.reshape(-1, 3) if need_tr else None, d_weight,
-                d_wb[:, 3].contiguous() if need_b else None, None, None, None, None)
+                d_wb[:, 3].contiguous() if need_b else None, None, None, None, None, None)
 
 
 def decode_gaussians_autograd(tokens, points, transl, weight, bias, C: int, R: int, radius: float,
-                              token_major: bool = False) -> Dict[str, torch.Tensor]:
+                              token_major: bool = False, order: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
     xyz, scale, rot, opacity, color = DecodeFunction.apply(tokens, points, transl, weight, bias, int(C), int(R), float(radius),
-                                                           bool(token_major))
+                                                           bool(token_major), order)
     return {"xyz": xyz, "scale": scale, "rot": rot, "opacity": opacity, "color": color, "shs": color}
 
 
@@ -397,7 +397,24 @@ def lbs_vertices(body: BodyModel, full_pose: torch.Tensor, shape_comp: torch.Ten
     return lbs_forward(body, full_pose, shape_comp)
 
 
-def densify_sites(verts: torch.Tensor, par: torch.Tensor, wgt: torch.Tensor) -> torch.Tensor:
+def densify_sites(verts: torch.Tensor, par: torch.Tensor, wgt: torch.Tensor, order: Optional[torch.Tensor] = None) -> torch.Tensor:
     if torch.is_grad_enabled() and verts.requires_grad:
         return DensifyFunction.apply(verts, par, wgt)
-    return densify_gather(verts, par, wgt)
+    return densify_gather(verts, par, wgt, order)
+
+
+def locality_order(rest_sites: torch.Tensor, extent: float) -> torch.Tensor:
+    """Processing order for the per-site kernels: Morton (Z-curve) order of the rest-pose site positions [N,3] inside
+    [-extent, extent]^3, 10 bits per axis.  int32 [N] on the sites' device; a permutation, so results do not depend on it."""
+    q = ((rest_sites / extent).clamp(-1, 1) * 0.5 + 0.5) * 1023.0
+    q = q.to(torch.int64).clamp(0, 1023)
+
+    def spread(v):                                   # 10 bits -> every third bit
+        v = (v | (v << 16)) & 0x030000FF
+        v = (v | (v << 8)) & 0x0300F00F
+        v = (v | (v << 4)) & 0x030C30C3
+        v = (v | (v << 2)) & 0x09249249
+        return v
+
+    code = spread(q[:, 0]) | (spread(q[:, 1]) << 1) | (spread(q[:, 2]) << 2)
+    return torch.argsort(code, stable=True).to(torch.int32).contiguous()

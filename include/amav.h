@@ -86,10 +86,13 @@ int amav_triplane_project_tm(int F, int C, int R, const float *tokens_tm, int64_
  *   outputs (the `gaussians` dict of renderer.py:337-344, each [F,N,k]):
  *   xyz[3] = points+offset+transl, scale[3] raw, rot[4] normalised (eps 1e-12), opacity[1] raw,
  *   color[3] = sigmoid(shs).
+ *   order [N] int32 or NULL: a permutation of the site indices; thread group i processes site order[i] (results are
+ *   written at the site's own index, so the output does not depend on it).  A locality order fixed at set-up (Morton
+ *   order of the rest-pose sites) lets neighbouring lanes share texels; the reference's randperm order shares none.
  */
 int amav_sample_decode(int F, int N, int C, int R, float radius, const float *proj, const float *points,
                        const float *transl, const float *weight, const float *bias,
-                       float *xyz, float *scale, float *rot, float *opacity, float *color, void *stream);
+                       float *xyz, float *scale, float *rot, float *opacity, float *color, const int32_t *order, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Stage 3: SMPL-X forward (smplx==0.1.28 SMPLX.forward -> lbs.lbs; call site renderer.py:261-274)
@@ -128,9 +131,9 @@ int amav_lbs_forward_6d(int F, int V, int J, int S, const float *pose_6d, const 
                         float *verts, void *stream);
 
 /* sites[f][i] = sum_k wgt[i][k] * verts[f][par[i][k]], k < P (flattened SubdivideMeshes levels +
- * randperm subset, renderer.py:280-288).  P = 1 with wgt = 1 is the plain gather. */
+ * randperm subset, renderer.py:280-288).  P = 1 with wgt = 1 is the plain gather.  order: as in amav_sample_decode. */
 int amav_densify_gather(int F, int V, int N, int P, const float *verts, const int32_t *par,
-                        const float *wgt, float *sites, void *stream);
+                        const float *wgt, float *sites, const int32_t *order, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Stage 4: tile-based Gaussian splatting (diff_gaussian_rasterization forward as called at

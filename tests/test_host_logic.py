@@ -55,7 +55,8 @@ def test_every_header_symbol_has_a_ctypes_signature():
     import re
     src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "amav.h")).read()
     declared = set(re.findall(r"\b(amav_[a-z0-9_]+)\s*\(", src))
-    special = {"amav_last_error", "amav_version", "amav_launch_count", "amav_splat_scan_tmp_elems", "amav_splat_scan_order_offset"}
+    special = {"amav_last_error", "amav_version", "amav_launch_count", "amav_splat_scan_tmp_elems", "amav_splat_scan_order_offset",
+               "amav_triplane_project_tc_scratch_elems"}
     assert declared - special == set(_lib._SIGS), (declared - special) ^ set(_lib._SIGS)
     for name in ("amav_lbs_forward_6d", "amav_lbs_backward_6d", "amav_triplane_project_tm", "amav_triplane_project_backward_tm",
                  "amav_frames_to_u8"):

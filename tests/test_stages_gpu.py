@@ -151,3 +151,25 @@ def test_tensor_core_projection_matches_float64_and_ffma(C, R, F):
     assert err_tc <= 2e-5, err_tc
     assert err_ffma <= 2e-6, err_ffma           # (the tensor core accumulates with truncation: ~1e-5, the FMA kernel ~3e-7)
     assert float(a[..., 11].abs().max()) == 0.0 and float(a[..., 15].abs().max()) == 0.0
+
+
+def test_locality_order_does_not_change_results():
+    """amav_sample_decode / amav_densify_gather with a processing order (Morton order of the rest-pose sites) write the
+    same bits at the same indices as without one."""
+    from audio_motion_avatar_b200 import stages, synthetic as S
+    g = torch.Generator().manual_seed(7)
+    F, N, C, R, V = 3, 5000, 64, 16, 700
+    verts = torch.randn(F, V, 3, generator=g).cuda() * 0.4
+    par = torch.randint(0, V, (N, 4), generator=g, dtype=torch.int32).cuda()
+    wgt = torch.rand(N, 4, generator=g).cuda()
+    order = stages.locality_order(stages.densify_gather(verts[:1], par, wgt)[0], 1.4)
+    assert sorted(order.cpu().tolist()) == list(range(N))
+    a, b = stages.densify_gather(verts, par, wgt), stages.densify_gather(verts, par, wgt, order)
+    assert torch.equal(a, b)
+    wd = S.make_decoder_weights(C, seed=3)
+    W = torch.cat([wd[f"{n}_layer.weight"] for n in ("xyz", "rotation", "scaling", "opacity", "shs")], 0).cuda()
+    bias = torch.cat([wd[f"{n}_layer.bias"] for n in ("xyz", "rotation", "scaling", "opacity", "shs")], 0).cuda()
+    proj = stages.triplane_project(torch.randn(F, C, 3 * R * R, generator=g).cuda(), W, C, R)
+    tr = torch.randn(F, 3, generator=g).cuda()
+    x, y = stages.sample_decode(proj, a, tr, W, bias, C, R, 1.4), stages.sample_decode(proj, a, tr, W, bias, C, R, 1.4, order=order)
+    assert all(torch.equal(x[k], y[k]) for k in ("xyz", "scale", "rot", "opacity", "color"))
