@@ -35,7 +35,7 @@ struct BlendBwdParams {
 
 constexpr int ACC_LD = 9;            // row stride of the smem accumulator (odd: conflict-free flush)
 
-__global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const BlendBwdParams p, const float *__restrict__ bg)
+__global__ void __launch_bounds__(BLEND_THREADS, 3) blend_bwd_kernel(const BlendBwdParams p, const float *__restrict__ bg)
 {
     // double-buffered batch state: thread t stages record t of a batch, zeroes its accumulator row and later flushes
     // it, so consecutive batches need ONE barrier between them (after staging); the flush of batch k overlaps the
@@ -55,13 +55,8 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
     const float alpha_min = 1.0f / 255.0f;
     const float ddelx_dx = 0.5f * (float)p.W, ddely_dy = 0.5f * (float)p.H;
     unsigned char *list = s_list[warp];
-    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4;
-    const int my_slot = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    const bool upper16 = lane & 16, upper8 = lane & 8, upper4 = lane & 4, upper2 = lane & 2, upper1 = lane & 1;
     const int64_t hw = (int64_t)p.H * p.W;
-    // after the split butterfly lanes 0, 4, ..., 28 hold the sums of values 0..7 (slot my_slot), every lane the ninth:
-    // lanes 0,4,..,28 and lane 1 add one value each to the batch accumulator in a single pass
-    const bool acc_writer = (lane & 3) == 0 || lane == 1;
-    const int acc_slot = lane == 1 ? 8 : my_slot;
     __shared__ float s_expc[4];
     const ExpConsts ec = exp_consts(s_expc);
 
@@ -157,80 +152,122 @@ __global__ void __launch_bounds__(BLEND_THREADS, 4) blend_bwd_kernel(const Blend
                 }
             }
             __syncwarp();
-            for (int k = cnt - 1; k >= 0; --k) {
-                const int j = list[k];
-                const float4 *rec = s_rec + 3 * j;
-                const float4 a = rec[0];
-                const float4 bq = rec[1];
-                const float dx = a.x - pxf, dy = a.y - pyf;
-                const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (bq.x * dy) * dy);
-                bool use = (before + j + 1 <= last_contributor) && power <= 0.0f && !(power < bq.z);
-                float G = 0.0f, alpha = 0.0f;
-                if (use) {
-                    G = amav_exp(power, ec);
-                    alpha = fminf(0.99f, bq.y * G);
-                    use = !(alpha < alpha_min);
-                }
-                if (!__any_sync(0xffffffffu, use)) continue;
-                float v[8], v8 = 0.0f;
+            // Back-to-front walk in GROUPS OF FOUR list entries: the four T / accum recurrences run one after the other
+            // (they are the sequential part), then the 4 x 8 per-pair terms are summed over the warp's 32 pixels by ONE
+            // 31-shuffle split butterfly (lane l ends with term l & 7 of entry l >> 3) and the four ninth terms by 6 more:
+            // 9.25 shuffles per entry instead of 19, one shared-memory atomic per lane, and the reductions of a group
+            // overlap the recurrences of the next.
+            for (int k = cnt - 1; k >= 0; k -= 4) {
+                float vals[32], nin[4];
+                int js[4];
+                bool any_use = false;
 #pragma unroll
-                for (int q = 0; q < 8; ++q) v[q] = 0.0f;
-                if (use) {
-                    const float4 c = rec[2];
-                    // 1 / (1 - alpha), 1 - alpha in [0.01, 1]: MUFU reciprocal (1 ulp) instead of upstream's
-                    // two IEEE divisions (10 instructions each); gradients are compared at 1e-3
-                    float inv_om;
-                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_om) : "f"(1.0f - alpha));
-                    T = T * inv_om;
-                    const float w = alpha * T;
-                    accum0 = fmaf(last_alpha, lc0, (1.0f - last_alpha) * accum0); lc0 = bq.w;
-                    accum1 = fmaf(last_alpha, lc1, (1.0f - last_alpha) * accum1); lc1 = c.x;
-                    accum2 = fmaf(last_alpha, lc2, (1.0f - last_alpha) * accum2); lc2 = c.y;
-                    float dL_dalpha = (lc0 - accum0) * g0;
-                    dL_dalpha = fmaf(lc1 - accum1, g1, dL_dalpha);
-                    dL_dalpha = fmaf(lc2 - accum2, g2, dL_dalpha);
-                    dL_dalpha = dL_dalpha * T;
-                    last_alpha = alpha;
-                    dL_dalpha = fmaf(-T_final * inv_om, bg_dot, dL_dalpha);
-                    const float dL_dG = bq.y * dL_dalpha;
-                    const float gdx = G * dx, gdy = G * dy;
-                    // conic = (-2 Ah, -Bn, -2 Ch): dG/ddelx = -gdx*conic.x - gdy*conic.y
-                    const float dG_ddelx = fmaf(2.0f * a.z, gdx, a.w * gdy);
-                    const float dG_ddely = fmaf(2.0f * bq.x, gdy, a.w * gdx);
-                    const float hq = -0.5f * dL_dG;
-                    v[0] = dL_dG * dG_ddelx * ddelx_dx;
-                    v[1] = dL_dG * dG_ddely * ddely_dy;
-                    v[2] = hq * gdx * dx;
-                    v[3] = hq * gdx * dy;
-                    v[4] = hq * gdy * dy;
-                    v[5] = G * dL_dalpha;
-                    v[6] = w * g0;
-                    v[7] = w * g1;
-                    v8 = w * g2;
+                for (int e = 0; e < 4; ++e) {
+                    js[e] = k - e >= 0 ? (int)list[k - e] : -1;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) vals[8 * e + q] = 0.0f;
+                    nin[e] = 0.0f;
+                    if (js[e] < 0) continue;                       // uniform across the warp
+                    const int j = js[e];
+                    const float4 *rec = s_rec + 3 * j;
+                    const float4 a = rec[0];
+                    const float4 bq = rec[1];
+                    const float dx = a.x - pxf, dy = a.y - pyf;
+                    const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (bq.x * dy) * dy);
+                    bool use = (before + j + 1 <= last_contributor) && power <= 0.0f && !(power < bq.z);
+                    float G = 0.0f, alpha = 0.0f;
+                    if (use) {
+                        G = amav_exp(power, ec);
+                        alpha = fminf(0.99f, bq.y * G);
+                        use = !(alpha < alpha_min);
+                    }
+                    if (use) {
+                        any_use = true;
+                        const float4 c = rec[2];
+                        // 1 / (1 - alpha), 1 - alpha in [0.01, 1]: MUFU reciprocal (1 ulp) instead of upstream's
+                        // two IEEE divisions (10 instructions each); gradients are compared at 1e-3
+                        float inv_om;
+                        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_om) : "f"(1.0f - alpha));
+                        T = T * inv_om;
+                        const float w = alpha * T;
+                        accum0 = fmaf(last_alpha, lc0, (1.0f - last_alpha) * accum0); lc0 = bq.w;
+                        accum1 = fmaf(last_alpha, lc1, (1.0f - last_alpha) * accum1); lc1 = c.x;
+                        accum2 = fmaf(last_alpha, lc2, (1.0f - last_alpha) * accum2); lc2 = c.y;
+                        float dL_dalpha = (lc0 - accum0) * g0;
+                        dL_dalpha = fmaf(lc1 - accum1, g1, dL_dalpha);
+                        dL_dalpha = fmaf(lc2 - accum2, g2, dL_dalpha);
+                        dL_dalpha = dL_dalpha * T;
+                        last_alpha = alpha;
+                        dL_dalpha = fmaf(-T_final * inv_om, bg_dot, dL_dalpha);
+                        const float dL_dG = bq.y * dL_dalpha;
+                        const float gdx = G * dx, gdy = G * dy;
+                        // conic = (-2 Ah, -Bn, -2 Ch): dG/ddelx = -gdx*conic.x - gdy*conic.y
+                        const float dG_ddelx = fmaf(2.0f * a.z, gdx, a.w * gdy);
+                        const float dG_ddely = fmaf(2.0f * bq.x, gdy, a.w * gdx);
+                        const float hq = -0.5f * dL_dG;
+                        vals[8 * e + 0] = dL_dG * dG_ddelx * ddelx_dx;
+                        vals[8 * e + 1] = dL_dG * dG_ddely * ddely_dy;
+                        vals[8 * e + 2] = hq * gdx * dx;
+                        vals[8 * e + 3] = hq * gdx * dy;
+                        vals[8 * e + 4] = hq * gdy * dy;
+                        vals[8 * e + 5] = G * dL_dalpha;
+                        vals[8 * e + 6] = w * g0;
+                        vals[8 * e + 7] = w * g1;
+                        nin[e] = w * g2;
+                    }
                 }
-                // split butterfly: 8 values over 32 lanes in 4+2+1+1+1 shuffles, the ninth in 5
+                if (!__any_sync(0xffffffffu, any_use)) continue;
+                // 32 values over 32 lanes: 16 + 8 + 4 + 2 + 1 shuffles; lane l ends with the warp total of vals[l]
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const float send = upper16 ? vals[q] : vals[q + 16];
+                    const float keep = upper16 ? vals[q + 16] : vals[q];
+                    vals[q] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float send = upper8 ? vals[q] : vals[q + 8];
+                    const float keep = upper8 ? vals[q + 8] : vals[q];
+                    vals[q] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float send = upper16 ? v[q] : v[q + 4];
-                    const float keep = upper16 ? v[q + 4] : v[q];
-                    v[q] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                    const float send = upper4 ? vals[q] : vals[q + 4];
+                    const float keep = upper4 ? vals[q + 4] : vals[q];
+                    vals[q] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
                 }
 #pragma unroll
                 for (int q = 0; q < 2; ++q) {
-                    const float send = upper8 ? v[q] : v[q + 2];
-                    const float keep = upper8 ? v[q + 2] : v[q];
-                    v[q] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                    const float send = upper2 ? vals[q] : vals[q + 2];
+                    const float keep = upper2 ? vals[q + 2] : vals[q];
+                    vals[q] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
                 }
                 {
-                    const float send = upper4 ? v[0] : v[1];
-                    const float keep = upper4 ? v[1] : v[0];
-                    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                    const float send = upper1 ? vals[0] : vals[1];
+                    const float keep = upper1 ? vals[1] : vals[0];
+                    vals[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
                 }
-                v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
-                v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+                // the four ninth terms: lane l ends with the total of nin[l >> 3]
 #pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, d);
-                if (acc_writer) atomicAdd(&s_acc[j * ACC_LD + acc_slot], lane == 1 ? v8 : v[0]);
+                for (int q = 0; q < 2; ++q) {
+                    const float send = upper16 ? nin[q] : nin[q + 2];
+                    const float keep = upper16 ? nin[q + 2] : nin[q];
+                    nin[q] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+                }
+                {
+                    const float send = upper8 ? nin[0] : nin[1];
+                    const float keep = upper8 ? nin[1] : nin[0];
+                    nin[0] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
+                nin[0] += __shfl_xor_sync(0xffffffffu, nin[0], 4);
+                nin[0] += __shfl_xor_sync(0xffffffffu, nin[0], 2);
+                nin[0] += __shfl_xor_sync(0xffffffffu, nin[0], 1);
+                const int e_mine = lane >> 3;
+                const int j_mine = e_mine == 0 ? js[0] : e_mine == 1 ? js[1] : e_mine == 2 ? js[2] : js[3];
+                if (j_mine >= 0) {
+                    if (vals[0] != 0.0f) atomicAdd(&s_acc[j_mine * ACC_LD + (lane & 7)], vals[0]);
+                    if ((lane & 7) == 0 && nin[0] != 0.0f) atomicAdd(&s_acc[j_mine * ACC_LD + 8], nin[0]);
+                }
             }
         }
         __syncthreads();                                       // every warp is done with the last batch
