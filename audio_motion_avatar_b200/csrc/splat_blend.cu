@@ -19,6 +19,11 @@
 
 #include "blend_common.cuh"
 
+// row-store epilogue of the peer-gather instantiation: 1 = one TMA bulk store per 384-byte row, 0 = float4 stores
+#ifndef AMAV_ROWS_BULK_STORE
+#define AMAV_ROWS_BULK_STORE 1
+#endif
+
 namespace {
 
 using namespace amav_blend;
@@ -278,12 +283,26 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
             // multi-GPU gather, where `out_color` is another GPU's memory: NVLink moves full lines, not 12-byte pixels
             const int64_t hw = (int64_t)p.H * p.W;
             const int tx0 = tile0 - ty * p.gx;
+#if AMAV_ROWS_BULK_STORE
+            // one TMA bulk store (cp.async.bulk.global.shared::cta) per 384-byte row: the copy engine of the SM emits the
+            // peer writes as whole bursts instead of 24 float4 stores per row from the LSU
+            asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");      // s_out was written by ordinary stores
+            __syncthreads();
+            if (threadIdx.x < 16 && ty * 16 + (int)threadIdx.x < p.H) {
+                float *dst = p.out_color + ((int64_t)f * hw + (int64_t)(ty * 16 + threadIdx.x) * p.W + tx0 * 16) * 3;
+                const uint32_t src = (uint32_t)__cvta_generic_to_shared(s_out + threadIdx.x * 96);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], 384;\n" :: "l"(dst), "r"(src) : "memory");
+                asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+                asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");   // the source rows have been read
+            }
+#else
             for (int i = threadIdx.x; i < 16 * 24; i += FWD_THREADS) {
                 const int row = i / 24, q = i - row * 24;
                 if (ty * 16 + row < p.H)
                     reinterpret_cast<float4 *>(p.out_color + ((int64_t)f * hw + (int64_t)(ty * 16 + row) * p.W + tx0 * 16) * 3)[q] =
                         reinterpret_cast<const float4 *>(s_out + row * 96)[q];
             }
+#endif
             __syncthreads();                         // s_out is free for the next pair
         }
     }

@@ -160,63 +160,74 @@ __global__ void __launch_bounds__(BLEND_THREADS, 3) blend_bwd_kernel(const Blend
             for (int k = cnt - 1; k >= 0; k -= 4) {
                 float vals[32], nin[4];
                 int js[4];
+                // phase A (independent per entry: the four exp chains overlap): alpha, G and the accept decision
+                float4 ra[4], rb[4];
+                float2 rc[4];
+                float ddx[4], ddy[4], Gs[4], als[4];
+                bool uses[4];
                 bool any_use = false;
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     js[e] = k - e >= 0 ? (int)list[k - e] : -1;
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) vals[8 * e + q] = 0.0f;
-                    nin[e] = 0.0f;
-                    if (js[e] < 0) continue;                       // uniform across the warp
-                    const int j = js[e];
+                    const int j = max(js[e], 0);
                     const float4 *rec = s_rec + 3 * j;
-                    const float4 a = rec[0];
-                    const float4 bq = rec[1];
-                    const float dx = a.x - pxf, dy = a.y - pyf;
-                    const float power = fmaf(fmaf(a.w, dy, a.z * dx), dx, (bq.x * dy) * dy);
-                    bool use = (before + j + 1 <= last_contributor) && power <= 0.0f && !(power < bq.z);
-                    float G = 0.0f, alpha = 0.0f;
-                    if (use) {
-                        G = amav_exp(power, ec);
-                        alpha = fminf(0.99f, bq.y * G);
-                        use = !(alpha < alpha_min);
-                    }
-                    if (use) {
-                        any_use = true;
-                        const float4 c = rec[2];
-                        // 1 / (1 - alpha), 1 - alpha in [0.01, 1]: MUFU reciprocal (1 ulp) instead of upstream's
-                        // two IEEE divisions (10 instructions each); gradients are compared at 1e-3
-                        float inv_om;
-                        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_om) : "f"(1.0f - alpha));
-                        T = T * inv_om;
-                        const float w = alpha * T;
-                        accum0 = fmaf(last_alpha, lc0, (1.0f - last_alpha) * accum0); lc0 = bq.w;
-                        accum1 = fmaf(last_alpha, lc1, (1.0f - last_alpha) * accum1); lc1 = c.x;
-                        accum2 = fmaf(last_alpha, lc2, (1.0f - last_alpha) * accum2); lc2 = c.y;
-                        float dL_dalpha = (lc0 - accum0) * g0;
-                        dL_dalpha = fmaf(lc1 - accum1, g1, dL_dalpha);
-                        dL_dalpha = fmaf(lc2 - accum2, g2, dL_dalpha);
-                        dL_dalpha = dL_dalpha * T;
-                        last_alpha = alpha;
-                        dL_dalpha = fmaf(-T_final * inv_om, bg_dot, dL_dalpha);
-                        const float dL_dG = bq.y * dL_dalpha;
-                        const float gdx = G * dx, gdy = G * dy;
-                        // conic = (-2 Ah, -Bn, -2 Ch): dG/ddelx = -gdx*conic.x - gdy*conic.y
-                        const float dG_ddelx = fmaf(2.0f * a.z, gdx, a.w * gdy);
-                        const float dG_ddely = fmaf(2.0f * bq.x, gdy, a.w * gdx);
-                        const float hq = -0.5f * dL_dG;
-                        vals[8 * e + 0] = dL_dG * dG_ddelx * ddelx_dx;
-                        vals[8 * e + 1] = dL_dG * dG_ddely * ddely_dy;
-                        vals[8 * e + 2] = hq * gdx * dx;
-                        vals[8 * e + 3] = hq * gdx * dy;
-                        vals[8 * e + 4] = hq * gdy * dy;
-                        vals[8 * e + 5] = G * dL_dalpha;
-                        vals[8 * e + 6] = w * g0;
-                        vals[8 * e + 7] = w * g1;
-                        nin[e] = w * g2;
-                    }
+                    ra[e] = rec[0];
+                    rb[e] = rec[1];
+                    const float4 c = rec[2];
+                    rc[e] = make_float2(c.x, c.y);
+                    ddx[e] = ra[e].x - pxf;
+                    ddy[e] = ra[e].y - pyf;
+                    const float power = fmaf(fmaf(ra[e].w, ddy[e], ra[e].z * ddx[e]), ddx[e], (rb[e].x * ddy[e]) * ddy[e]);
+                    const bool inr = js[e] >= 0 && (before + j + 1 <= last_contributor) && power <= 0.0f && !(power < rb[e].z);
+                    // same exp as the forward on every accepted pair (power in [pmin, 0]); the clamp only keeps the
+                    // rejected lanes' garbage finite
+                    const float G = amav_exp(fminf(fmaxf(power, -80.0f), 0.0f), ec);
+                    const float alpha = fminf(0.99f, rb[e].y * G);
+                    uses[e] = inr && !(alpha < alpha_min);
+                    Gs[e] = uses[e] ? G : 0.0f;
+                    als[e] = uses[e] ? alpha : 0.0f;
+                    any_use |= uses[e];
                 }
                 if (!__any_sync(0xffffffffu, any_use)) continue;
+                // phase B (the sequential part, branch-free): T and the colour behind each entry, then the 9 terms.  A
+                // rejected pair has alpha = G = 0: T, accum, last colour stay, all its terms are 0.
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const bool use = uses[e];
+                    const float alpha = als[e], G = Gs[e], dx = ddx[e], dy = ddy[e];
+                    // 1 / (1 - alpha), 1 - alpha in [0.01, 1]: MUFU reciprocal (1 ulp) instead of upstream's
+                    // two IEEE divisions (10 instructions each); gradients are compared at 1e-3
+                    float inv_om;
+                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv_om) : "f"(1.0f - alpha));
+                    T = T * inv_om;
+                    const float w = alpha * T;
+                    const float om = 1.0f - last_alpha;
+                    const float n0 = fmaf(last_alpha, lc0, om * accum0), n1 = fmaf(last_alpha, lc1, om * accum1),
+                                n2 = fmaf(last_alpha, lc2, om * accum2);
+                    accum0 = use ? n0 : accum0; accum1 = use ? n1 : accum1; accum2 = use ? n2 : accum2;
+                    lc0 = use ? rb[e].w : lc0; lc1 = use ? rc[e].x : lc1; lc2 = use ? rc[e].y : lc2;
+                    last_alpha = use ? alpha : last_alpha;
+                    float dL_dalpha = (lc0 - accum0) * g0;
+                    dL_dalpha = fmaf(lc1 - accum1, g1, dL_dalpha);
+                    dL_dalpha = fmaf(lc2 - accum2, g2, dL_dalpha);
+                    dL_dalpha = dL_dalpha * T;
+                    dL_dalpha = fmaf(-T_final * inv_om, bg_dot, dL_dalpha);
+                    const float dL_dG = rb[e].y * dL_dalpha;
+                    const float gdx = G * dx, gdy = G * dy;
+                    // conic = (-2 Ah, -Bn, -2 Ch): dG/ddelx = -gdx*conic.x - gdy*conic.y
+                    const float dG_ddelx = fmaf(2.0f * ra[e].z, gdx, ra[e].w * gdy);
+                    const float dG_ddely = fmaf(2.0f * rb[e].x, gdy, ra[e].w * gdx);
+                    const float hq = -0.5f * dL_dG;
+                    vals[8 * e + 0] = dL_dG * dG_ddelx * ddelx_dx;
+                    vals[8 * e + 1] = dL_dG * dG_ddely * ddely_dy;
+                    vals[8 * e + 2] = hq * gdx * dx;
+                    vals[8 * e + 3] = hq * gdx * dy;
+                    vals[8 * e + 4] = hq * gdy * dy;
+                    vals[8 * e + 5] = G * dL_dalpha;
+                    vals[8 * e + 6] = w * g0;
+                    vals[8 * e + 7] = w * g1;
+                    nin[e] = w * g2;
+                }
                 // 32 values over 32 lanes: 16 + 8 + 4 + 2 + 1 shuffles; lane l ends with the warp total of vals[l]
 #pragma unroll
                 for (int q = 0; q < 16; ++q) {

@@ -154,6 +154,54 @@ class PeerFrameGather:
         self.handle.barrier()                      # every rank's kernels (and their peer stores) are complete
         return self.local if self.rank == self.dst else None
 
+    def render_staged(self, render, tokens: torch.Tensor, cams: dict, params: dict, chunks: int = 4) -> Optional[torch.Tensor]:
+        """The same gather with the transfer taken OFF the blend kernel: the shard is rendered in ``chunks`` pieces into
+        local staging buffers (per-pixel stores, the fast local kernel) and every finished piece is pushed into the
+        destination's buffer by a peer copy on a second stream while the next piece renders.  Seven senders storing
+        384-byte row segments from inside the blend kernel reach ~520 GB/s into rank 0; plain peer copies reach ~795 GB/s
+        (tools/ingress_probe.py), and only the last piece's copy is exposed."""
+        n = self.stop - self.start
+        if tokens.shape[1] != n:
+            raise ValueError(f"rank {self.rank} holds {tokens.shape[1]} frames, its shard has {n}")
+        dev = tokens.device
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(dev)
+            self._staging = [None, None]
+            self._staged_free = [None, None]
+        cuts = chunk_bounds(n, chunks)
+        if self.rank == self.dst:
+            # the destination's own frames need no transfer: rendered straight into its buffer
+            if n:
+                with torch.no_grad():
+                    render(tokens, cams, None, params, out=self.local[self.start:self.stop])
+        else:
+            piece = max((cuts[i + 1] - cuts[i] for i in range(len(cuts) - 1)), default=0)
+            for k in range(len(cuts) - 1):
+                a, b = cuts[k], cuts[k + 1]
+                if b <= a:
+                    continue
+                slot = k & 1
+                if self._staging[slot] is None or self._staging[slot].shape[0] < piece:
+                    self._staging[slot] = torch.empty((piece,) + self.shape[1:], dtype=torch.float32, device=dev)
+                if self._staged_free[slot] is not None:
+                    main.wait_event(self._staged_free[slot])           # the copy of piece k - 2 has drained this buffer
+                stage = self._staging[slot][:b - a]
+                with torch.no_grad():
+                    render(tokens[:, a:b], {m: v[:, a:b] for m, v in cams.items()}, None, {m: v[:, a:b] for m, v in params.items()},
+                           out=stage)
+                done = torch.cuda.Event()
+                done.record(main)
+                with torch.cuda.stream(self._copy_stream):
+                    self._copy_stream.wait_event(done)
+                    self.target[self.start + a:self.start + b].copy_(stage, non_blocking=True)
+                    freed = torch.cuda.Event()
+                    freed.record(self._copy_stream)
+                self._staged_free[slot] = freed
+            main.wait_stream(self._copy_stream)
+        self.handle.barrier()
+        return self.local if self.rank == self.dst else None
+
     def capture(self, renderer, tokens: torch.Tensor, cams: dict, params: dict):
         """CUDA-graph this rank's shard render with the peer stores inside the graph (``Renderer.capture`` with
         ``out`` = this rank's slice of the destination buffer).  A 15-frame shard (120 frames over 8 GPUs) is ~2 ms of

@@ -61,8 +61,11 @@ def parse():
     ap.add_argument("--only", default="", help="comma list of secondary blocks to keep (graph,parity,latency,train,stress,weak,sink,yardsticks)")
     ap.add_argument("--gather-chunks", type=int, default=0,
                     help="N > 1, --gather nccl: pieces the shard is rendered and gathered in (0: 1 for N <= 2, else 4)")
-    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
-                    help="N > 1: blend kernels store into rank 0's buffer over NVLink (symmetric memory), or NCCL send/recv")
+    ap.add_argument("--gather", default="auto", choices=["auto", "staged", "peer", "nccl"],
+                    help="N > 1: peer = the blend kernels store into rank 0's symmetric buffer themselves (one launch sequence per "
+                         "shard); staged = local render in >= 30-frame pieces + peer copies on a second stream (many senders, long "
+                         "shards: 7 -> 1 row-segment stores reach ~520 GB/s, plain peer copies ~795 GB/s); auto = staged when "
+                         "N >= 4 and a shard has >= 60 frames, else peer; nccl = NCCL send/recv")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "train"],
                     help="sequence = the default line; train = configs[3] alone as its own line")
     ap.add_argument("--loss", default="l1_ssim", choices=["l1_ssim", "l1_torch"],
@@ -685,9 +688,12 @@ def run_ours(args):
     def make_gather(frames_total):
         """(peer, buffer, mode) for a gather of `frames_total` frames on rank 0."""
         peer, buf, mode = None, None, "none"
+        want_mode = args.gather
+        if want_mode == "auto":
+            want_mode = "staged" if world >= 4 and frames_total // world >= 60 else "peer"
         if world > 1 and not args.no_gather:
             mode = "nccl"
-            if args.gather == "peer" and PeerFrameGather.available():
+            if want_mode in ("peer", "staged") and PeerFrameGather.available():
                 try:
                     peer = PeerFrameGather(frames_total, size, size, dev, dst=0)
                 except Exception as exc:                 # no peer access / allocator unavailable: NCCL send/recv instead
@@ -695,7 +701,7 @@ def run_ours(args):
                 ok = torch.tensor([1.0 if peer is not None else 0.0], device=dev)
                 dist.all_reduce(ok, op=dist.ReduceOp.MIN)            # every rank takes the same path
                 if ok.item() > 0:
-                    mode = "peer"
+                    mode = want_mode
                 else:
                     peer = None
             if peer is None and rank == 0:
@@ -703,12 +709,16 @@ def run_ours(args):
         return peer, buf, mode
 
     chunks = args.gather_chunks if args.gather_chunks > 0 else (1 if world <= 2 else 4)
+    stage_chunks = lambda frames: args.gather_chunks if args.gather_chunks > 0 else max(1, frames // 30)
 
-    def make_step(peer, buf, tok, cm, pr, frames_total, chk_box):
+    def make_step(peer, buf, tok, cm, pr, frames_total, chk_box, mode):
         def step():
             with deferred_overflow_checks() as chk:      # overflow flags are read once, after the timed region
-                if peer is not None:
-                    # frame gather (north_star) fused into the blend kernel: pixels are stored into rank 0's buffer over NVLink
+                if peer is not None and mode == "staged":
+                    # frame gather (north_star): pieces rendered locally, pushed to rank 0 by peer copies while the next renders
+                    peer.render_staged(r, tok, cm, pr, chunks=stage_chunks(tok.shape[1]))
+                elif peer is not None:
+                    # frame gather fused into the blend kernel: pixels are stored into rank 0's buffer over NVLink
                     peer.render(r, tok, cm, pr)
                 elif world > 1 and not args.no_gather:
                     render_and_gather(r, tok, cm, pr, frames_total, chunks=chunks, dst=0, out=buf)
@@ -721,7 +731,7 @@ def run_ours(args):
     # ---- headline: configs[1] (N = 1) / configs[2] strong split (N > 1) ----
     peer, gather_buf, gather_mode = make_gather(Ftot)
     box = {}
-    step = make_step(peer, gather_buf, tokens, cams_d, params_d, Ftot, box)
+    step = make_step(peer, gather_buf, tokens, cams_d, params_d, Ftot, box, gather_mode)
     ms_per_step, clocks, launches = ctx.timed(step, steps, warmup)
     overflow = bool(box["chk"].overflowed())
     if world > 1:
@@ -731,6 +741,7 @@ def run_ours(args):
     value = Ftot / (ms_per_step * 1e-3)
     per_stage, stages_ms, D, peak, peak_src = stage_table(r, tokens, cams_d, params_d, Fr, N, size)
     par = f"frame-sharded x{world}" + {"none": "", "peer": " + frame gather to rank 0 by peer stores from the blend kernel (symmetric memory over NVLink)",
+                                        "staged": " + frame gather to rank 0: pieces rendered locally, peer copies into rank 0's symmetric buffer on a second stream",
                                         "nccl": f" + NCCL frame gather to rank 0 overlapped with the render ({chunks} pieces)"}[gather_mode]
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
@@ -742,7 +753,7 @@ def run_ours(args):
             "roofline": roofline_block(per_stage, stages_ms, D, peak, peak_src, Fr, N, size, ms_per_step)}
 
     # the same step as ONE CUDA-graph launch per rank (Renderer.capture); at N > 1 the peer stores are inside the graph
-    if want("graph") and (world == 1 or peer is not None):
+    if want("graph") and (world == 1 or (peer is not None and gather_mode == "peer")):
         try:
             if peer is not None:
                 gobj = peer.capture(r, tokens, cams_d, params_d)
@@ -785,7 +796,7 @@ def run_ours(args):
         wpar_d, wcam_d = {k: v.to(dev) for k, v in wpar.items()}, {k: v.to(dev) for k, v in wcam.items()}
         wpeer, wbuf, wmode = make_gather(world * Ftot)
         wbox = {}
-        wstep = make_step(wpeer, wbuf, wtok, wcam_d, wpar_d, world * Ftot, wbox)
+        wstep = make_step(wpeer, wbuf, wtok, wcam_d, wpar_d, world * Ftot, wbox, wmode)
         wms, wclk, _ = ctx.timed(wstep, steps, warmup)
         line["weak"] = {"value": world * Ftot / (wms * 1e-3), "unit": UNIT, "ms_per_step": wms, "frames_per_rank": Ftot,
                         "frames_total": world * Ftot, "scaling": "weak", "gather": wmode, "clocks": wclk,

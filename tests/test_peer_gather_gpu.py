@@ -45,6 +45,16 @@ def _worker(rank, world, port, q):
         torch.cuda.synchronize()
         if rank == 0:
             ok = ok and out2 is not None and torch.equal(out2, full[0])
+        # staged variant: local render in pieces + peer copies on a second stream
+        if rank == 0:
+            peer.local.zero_()
+        dist.barrier()
+        for _ in range(2):
+            out4 = peer.render_staged(r, tk, cm, pr, chunks=2)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            ok = ok and out4 is not None and torch.equal(out4, full[0])
         # the same shard step as one CUDA graph with the peer stores inside (PeerFrameGather.capture)
         if rank == 0:
             peer.local.zero_()
