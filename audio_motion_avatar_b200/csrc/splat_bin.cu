@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_spine(uint32_t *block_sums,
 {
     if (threadIdx.x == 0) { block_sums[nb + 1] = 0u; block_sums[nb + 2] = 0u; }      // deep-tile list counters
     uint32_t carry = 0, zcarry = 0;
+    bool wrapped = false;                                 // the 32-bit entry count of the call overflowed
     for (int base = 0; base < nb; base += SCAN_THREADS) {
         const int i = base + threadIdx.x;
         const uint32_t v = i < nb ? block_sums[i] : 0u, z = i < nb ? ne_sums[i] : 0u;
@@ -77,10 +78,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_spine(uint32_t *block_sums,
         const uint32_t ex = block_exclusive_scan(v, total);
         const uint32_t zex = block_exclusive_scan(z, ztotal);
         if (i < nb) { block_sums[i] = carry + ex; ne_sums[i] = zcarry + zex; }
+        wrapped |= carry + total < carry;
         carry += total;
         zcarry += ztotal;
     }
-    if (threadIdx.x == 0) { block_sums[nb] = carry; *ne_count = zcarry; }
+    // D = 0xffffffff is the "too many entries for one call" sentinel: the host raises on it, the scatter kernel sets the
+    // overflow flag (a wrapped scan would otherwise scatter into the wrong buckets without any sign)
+    if (threadIdx.x == 0) { block_sums[nb] = (wrapped || carry == 0xffffffffu) ? 0xffffffffu : carry; *ne_count = zcarry; }
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t *__restrict__ count, int64_t n,
@@ -140,6 +144,7 @@ __global__ void __launch_bounds__(256, 3) scatter_entries(int N, int gx, int til
 {
     extern __shared__ uint32_t s_pos[];
     const int f = blockIdx.y;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && tile_start[(int64_t)gridDim.y * tiles] == 0xffffffffu) *overflow = 1;
     const int64_t tbase = (int64_t)f * tiles;
     ushort4 rc[SCAT_PER];
     float depth[SCAT_PER];                                   // fetched up front: the loads overlap the histogram phases

@@ -115,6 +115,9 @@ def splat_forward(means3d: torch.Tensor, scales: torch.Tensor, rots: torch.Tenso
         D = -1
     else:
         D = int(tile_start[nt].item()) & 0xFFFFFFFF
+        if D == 0xFFFFFFFF:
+            raise _lib.AmavError("more than 2^32 - 2 (Gaussian, tile) entries in one call: the 32-bit tile offsets cannot "
+                                 "address them; render fewer frames per call")
         ws.ensure_capacity(D, dev)
         ws.last_D = D
         ws.per_frame[(N, height, width, views_per_set)] = D / max(F, 1)

@@ -196,3 +196,24 @@ def test_row_store_variant_equals_per_pixel_stores(W, H):
     assert (ref != torch.tensor([0.2, 0.5, 0.9], device=d)).any()          # something was actually rendered
     with pytest.raises(AmavError):
         run(True, width=W + 8)
+
+
+def test_scan_flags_a_wrapped_entry_count():
+    """tile offsets are 32-bit: a call whose entry count reaches 2^32 must not wrap silently.  The scan writes
+    the sentinel D = 0xffffffff, on which splat_forward raises and the scatter kernel sets the overflow flag."""
+    from audio_motion_avatar_b200 import _lib
+    from audio_motion_avatar_b200._lib import SplatDims, call, ptr, stream_ptr
+    d = torch.device("cuda:0")
+    W = H = 64                                                  # 16 tiles per frame, 2 frames
+    dims = SplatDims(2, 1, 1, W, H, 0, 1.0)
+    nt = 32
+    count = torch.full((nt,), 150_000_000, dtype=torch.int32, device=d)          # 32 x 1.5e8 = 4.8e9 > 2^32
+    start = torch.zeros(nt + 1, dtype=torch.int32, device=d)
+    tmp = torch.zeros(int(_lib.lib().amav_splat_scan_tmp_elems(nt)), dtype=torch.int32, device=d)
+    call("amav_splat_scan", dims, ptr(count), ptr(start), ptr(tmp), stream_ptr())
+    torch.cuda.synchronize()
+    assert int(start[nt].item()) & 0xFFFFFFFF == 0xFFFFFFFF
+    count.fill_(1000)
+    call("amav_splat_scan", dims, ptr(count), ptr(start), ptr(tmp), stream_ptr())
+    torch.cuda.synchronize()
+    assert int(start[nt].item()) == 32000 and int(start[5].item()) == 5000
