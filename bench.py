@@ -65,7 +65,7 @@ def parse():
                     help="N > 1: peer = the blend kernels store into rank 0's symmetric buffer themselves (one launch sequence per "
                          "shard); staged = local render in >= 30-frame pieces + peer copies on a second stream (many senders, long "
                          "shards: 7 -> 1 row-segment stores reach ~520 GB/s, plain peer copies ~795 GB/s); auto = staged when "
-                         "N >= 4 and a shard has >= 60 frames, else peer; nccl = NCCL send/recv")
+                         "N >= 8 and a shard has >= 60 frames, else peer; nccl = NCCL send/recv")
     ap.add_argument("--workload", default="sequence", choices=["sequence", "train"],
                     help="sequence = the default line; train = configs[3] alone as its own line")
     ap.add_argument("--loss", default="l1_ssim", choices=["l1_ssim", "l1_torch"],
@@ -690,7 +690,9 @@ def run_ours(args):
         peer, buf, mode = None, None, "none"
         want_mode = args.gather
         if want_mode == "auto":
-            want_mode = "staged" if world >= 4 and frames_total // world >= 60 else "peer"
+            # fused row stores take ~520 GB/s into rank 0 from many senders: they stay hidden behind a shard's render up to
+            # N = 4 (3 x 1.5 GB = 8.7 ms < 14 ms); at N = 8 (10.6 GB = 20 ms) the staged copies (~795 GB/s) win
+            want_mode = "staged" if world >= 8 and frames_total // world >= 60 else "peer"
         if world > 1 and not args.no_gather:
             mode = "nccl"
             if want_mode in ("peer", "staged") and PeerFrameGather.available():
