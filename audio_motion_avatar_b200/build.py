@@ -24,6 +24,7 @@ SOURCES = [
     ("triplane_tm.cu", []),
     ("triplane_tc.cu", []),
     ("lbs.cu", []),
+    ("lbs_tc.cu", []),
     ("lbs_bwd.cu", []),
     ("image_loss.cu", []),
     ("camera.cu", ["-fmad=false"]),

@@ -41,4 +41,8 @@ cudaError_t amav_ensure_dyn_smem(const void *func, int bytes);
         amav_count_launches(1);                                                     \
     } while (0)
 
+// tensor-core form of the pose/shape blend of the SMPL-X forward (lbs_tc.cu); 0 on success
+int amav_pose_blend_tc(int F, int V, int S, int K, const float *pose_feature, const float *shape_comp, const float *v_template,
+                       const float *shapedirs, const float *posedirs, float *v_posed, cudaStream_t stream);
+
 static inline int amav_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }

@@ -12,6 +12,11 @@
 // `transl` is NOT applied here (renderer.py:248-249,271); covariances are never skinned.
 #include "common.cuh"
 
+// 1: the pose/shape blend runs on the tensor cores (lbs_tc.cu); 0: the FP32-FMA pose_blend_kernel below
+#ifndef AMAV_POSE_BLEND_TC
+#define AMAV_POSE_BLEND_TC 1
+#endif
+
 namespace {
 
 constexpr int MAXJ = 64;
@@ -158,6 +163,7 @@ __global__ void __launch_bounds__(64) lbs_pose_kernel(int J, int S, const float 
 }
 
 // ---------------------------------------------------------------------------------------------
+#if !AMAV_POSE_BLEND_TC
 // v_posed[f][v] = v_template[v] + shapedirs[v].shape_comp[f] + pose_feature[f].posedirs[:, 3v:3v+3]
 // Thread = vertex (3 columns), CTA = 128 vertices x PB_F frames; pose features of the frame group in
 // shared memory as [k][PB_F] so one LDS.128 feeds four frames.
@@ -230,6 +236,7 @@ __global__ void __launch_bounds__(PB_THREADS) pose_blend_kernel(int F, int V, in
         }
     }
 }
+#endif  // !AMAV_POSE_BLEND_TC
 
 // verts[f][v] = (sum_j W[v][j] A[f][j]) . [v_posed; 1]; zero weights are skipped (adding w*A = 0 is exact, so
 // the dense sum in joint order is unchanged).
@@ -339,12 +346,21 @@ static int lbs_forward_impl(bool sixd, int F, int V, int J, int S, const float *
         lbs_pose_kernel<true><<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, pose_feature, joints, A);
     else
         lbs_pose_kernel<false><<<F, 64, 0, stream>>>(J, S, full_pose, shape_comp, J_template, J_dirs, parents, pose_feature, joints, A);
+#if AMAV_POSE_BLEND_TC
+    // v_posed on the tensor cores (lbs_tc.cu: tcgen05.mma kind::tf32, 3xTF32, TMEM accumulator)
+    AMAV_CHECK_ARG(F <= 65535 * 128, "F too large for one call");
+    if (amav_pose_blend_tc(F, V, S, K, pose_feature, shape_comp, v_template, shapedirs, posedirs, v_posed, stream) != 0) {
+        amav_set_error("%s: pose_blend_tc launch failed", __func__);
+        return AMAV_ECUDA;
+    }
+#else
     const size_t smem = (size_t)(K + S) * PB_F * sizeof(float);
     AMAV_CHECK_ARG(smem <= 200 * 1024, "pose basis too large");
     amav_ensure_dyn_smem((const void *)pose_blend_kernel, (int)smem);
     dim3 gb(amav_div_up(V, PB_THREADS), amav_div_up(F, PB_F));
     pose_blend_kernel<<<gb, PB_THREADS, smem, stream>>>(F, V, S, K, pose_feature, shape_comp, v_template, shapedirs,
                                                         posedirs, v_posed);
+#endif
     AMAV_CHECK_ARG(F <= 65535, "F too large for one call");
     dim3 gs(amav_div_up(V, 256), F);
     skin_kernel<<<gs, 256, 0, stream>>>(V, J, weights_T, A, v_posed, verts);
