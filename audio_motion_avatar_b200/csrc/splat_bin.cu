@@ -62,7 +62,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums(const uint32_t *
     uint32_t total, ztotal;
     block_exclusive_scan(s, total);
     block_exclusive_scan(z, ztotal);
-    if (threadIdx.x == 0) { block_sums[blockIdx.x] = total; ne_sums[blockIdx.x] = ztotal; }
+    // did the block's entry count leave 32 bits?  (a 16-bit digest of the high part is enough: counts are < 2^31 each)
+    uint32_t hi = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k)
+        if (base + k < n) hi += count[base + k] >> 16;
+    uint32_t hitotal;
+    block_exclusive_scan(hi, hitotal);
+    if (threadIdx.x == 0) {
+        block_sums[blockIdx.x] = total;
+        // the low halves of 1024 counts add up to < 2^26, so a total >= 2^32 needs the high halves to reach 2^16 - 2^10
+        ne_sums[blockIdx.x] = ztotal | (hitotal >= 0xfc00u ? 0x80000000u : 0u);
+    }
 }
 
 // Single block: in-place exclusive scan of block_sums[0..nb); block_sums[nb] = grand total.
@@ -73,7 +84,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_spine(uint32_t *block_sums,
     bool wrapped = false;                                 // the 32-bit entry count of the call overflowed
     for (int base = 0; base < nb; base += SCAN_THREADS) {
         const int i = base + threadIdx.x;
-        const uint32_t v = i < nb ? block_sums[i] : 0u, z = i < nb ? ne_sums[i] : 0u;
+        const uint32_t v = i < nb ? block_sums[i] : 0u, zraw = i < nb ? ne_sums[i] : 0u;
+        const uint32_t z = zraw & 0x7fffffffu;
+        wrapped |= __syncthreads_or((int)(zraw >> 31)) != 0;
         uint32_t total, ztotal;
         const uint32_t ex = block_exclusive_scan(v, total);
         const uint32_t zex = block_exclusive_scan(z, ztotal);
