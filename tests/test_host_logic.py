@@ -61,3 +61,35 @@ def test_every_header_symbol_has_a_ctypes_signature():
     for name in ("amav_lbs_forward_6d", "amav_lbs_backward_6d", "amav_triplane_project_tm", "amav_triplane_project_backward_tm",
                  "amav_frames_to_u8"):
         assert name in declared
+
+
+def test_training_jobs_split_covers_every_render_once():
+    """bench.train_jobs: the 16 (subject, view) jobs of configs[3] over 1/2/4/8/16 ranks -- contiguous subject-major blocks,
+    every job exactly once, equal shares."""
+    import bench
+    B, Tv = 4, 4
+    for world in (1, 2, 4, 8, 16):
+        seen = []
+        for rank in range(world):
+            subj, views = bench.train_jobs(rank, world, B, Tv)
+            assert subj == list(range(subj[0], subj[-1] + 1)) and views == list(range(views[0], views[-1] + 1))
+            seen += [(s, v) for s in subj for v in views]
+            assert len(subj) * len(views) == B * Tv // world
+        assert sorted(seen) == [(s, v) for s in range(B) for v in range(Tv)]
+    assert bench.train_jobs(3, 8, B, Tv, per_rank_all=True) == (list(range(B)), list(range(Tv)))
+
+
+def test_strong_split_frames_are_the_same_sequence():
+    """bench.synthetic_inputs: frames [f0, f1) cut by any rank are the frames of the one 120-frame sequence (poses and
+    cameras; the tokens are seeded per frame index on the device, covered by the N > 1 gather_check)."""
+    import bench
+    import torch
+    from audio_motion_avatar_b200 import synthetic as S
+    from audio_motion_avatar_b200.shard import frame_shard
+    whole = S.make_pose_sequence(1, 120, seed=0)
+    for world in (2, 8):
+        for rank in (0, world - 1):
+            f0, f1 = frame_shard(120, rank, world)
+            part = {k: v[:, f0:f1] for k, v in S.make_pose_sequence(1, 120, seed=0).items()}
+            assert all(torch.equal(part[k], whole[k][:, f0:f1]) for k in whole)
+    assert sum(frame_shard(120, r, 8)[1] - frame_shard(120, r, 8)[0] for r in range(8)) == 120
