@@ -26,6 +26,7 @@ class SplatDims(ctypes.Structure):
 _SIGS = {
     "amav_triplane_project": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
     "amav_triplane_project_tc": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p],
+    "amav_triplane_project_tc_static": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
     "amav_triplane_project_tm": [c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p],
     "amav_sample_decode": [c_int, c_int, c_int, c_int, c_float] + [c_void_p] * 11 + [c_void_p],
     "amav_lbs_precompute": [c_int, c_int, c_int] + [c_void_p] * 7 + [c_void_p],

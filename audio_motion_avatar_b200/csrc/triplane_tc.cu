@@ -19,6 +19,8 @@
 // issue slots: 3.5 instructions per token element instead of 14 FFMAs.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace {
 
 __constant__ int c_slot_row_tc[16] = {3, 4, 5, 6, 0, 1, 2, 10, 7, 8, 9, -1, 11, 12, 13, -1};
@@ -203,6 +205,74 @@ extern "C" int amav_triplane_project_tc(int F, int C, int R, const float *tokens
     const int64_t grid = (int64_t)F * 3 * (R * R / TC_TEX);
     AMAV_CHECK_ARG(grid < ((int64_t)1 << 31), "too many tiles");
     project_tc_kernel<<<(unsigned)grid, TC_THREADS, TC_SMEM, stream>>>(C, R * R, tokens, token_frame_stride, wprep_scratch, proj);
+    AMAV_CHECK_LAUNCH();
+    return AMAV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (no counterpart in the reference): the split
+// weights live in a file-scope device array instead of caller-owned scratch, for callers that cannot allocate (CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc).  192 KB per GPU that loads the library, held
+// until exit.  Every call shares the array: weight_prep_kernel rewrites all of the 3 (C/32) 1024 floats the projection
+// reads (nothing has to start at zero), and two calls that overlap on the GPU (different streams) race on it.
+constexpr int TC_STATIC_MAX_C = 512;
+constexpr int TC_STATIC_ELEMS = 3 * (TC_STATIC_MAX_C / TC_KB) * 1024;
+static __device__ __align__(256) float g_wprep_static[TC_STATIC_ELEMS];
+
+namespace {
+constexpr int TC_MAX_DEVICES = 64;
+std::mutex g_static_mu;
+float *g_static_ptr[TC_MAX_DEVICES] = {};
+
+// device address of g_wprep_static on the CURRENT device; the symbol's name in host code is only a handle, so the
+// address is looked up once per device (with that device current) and cached
+cudaError_t static_scratch(float **out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= TC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        float *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_wprep_static);
+        if (e != cudaSuccess) return e;
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int amav_triplane_project_tc_static(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
+                                               const float *weight, float *proj, void *stream_)
+{
+    AMAV_CHECK_ARG(F >= 0 && C > 0 && R > 0, "bad dims");
+    AMAV_CHECK_ARG(C <= TC_STATIC_MAX_C, "C exceeds the static scratch (512 channels max): use amav_triplane_project_tc with caller-owned scratch");
+    AMAV_CHECK_ARG((R * R) % TC_TEX == 0, "R*R must be a multiple of 128");
+    AMAV_CHECK_ARG(C % TC_KB == 0, "C must be a multiple of 32");
+    AMAV_CHECK_ARG(token_frame_stride >= (int64_t)C * 3 * R * R, "frame stride too small");
+    if (F == 0) return AMAV_OK;
+    AMAV_CHECK_ARG(tokens && weight && proj, "null buffer");
+    AMAV_CHECK_ARG(((uintptr_t)proj & 15) == 0, "buffers must be 16-byte aligned");
+    const int64_t grid = (int64_t)F * 3 * (R * R / TC_TEX);
+    AMAV_CHECK_ARG(grid < ((int64_t)1 << 31), "too many tiles");
+    float *wprep = nullptr;
+    cudaError_t e = static_scratch(&wprep);
+    if (e != cudaSuccess || !wprep) {
+        amav_set_error("%s: cudaGetSymbolAddress(static scratch) failed: %s", __func__, cudaGetErrorString(e));
+        return AMAV_ECUDA;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int n = 3 * (C / TC_KB) * 512;
+    weight_prep_kernel<<<amav_div_up(n, 256), 256, 0, stream>>>(C, weight, 3 + 3 * C, wprep);
+    AMAV_CHECK_LAUNCH();
+    e = amav_ensure_dyn_smem((const void *)project_tc_kernel, TC_SMEM);
+    if (e != cudaSuccess) {
+        amav_set_error("%s: cudaFuncSetAttribute failed: %s", __func__, cudaGetErrorString(e));
+        return AMAV_ECUDA;
+    }
+    project_tc_kernel<<<(unsigned)grid, TC_THREADS, TC_SMEM, stream>>>(C, R * R, tokens, token_frame_stride, wprep, proj);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }

@@ -71,6 +71,18 @@ int64_t amav_triplane_project_tc_scratch_elems(int C);
 int amav_triplane_project_tc(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
                              const float *weight, float *wprep_scratch, float *proj, void *stream);
 
+/* Allocation-free variant of amav_triplane_project_tc.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same inputs, output and arithmetic as amav_triplane_project_tc; the split-weight
+ * scratch is a file-scope device array of the library (192 KB, resident on every GPU that loads the library until the
+ * process exits) instead of a caller buffer, so C <= AMAV_TC_STATIC_MAX_C (larger C: AMAV_EINVAL with a message naming
+ * the limit).  The call makes no cudaMalloc / cudaFree / allocating library call.  Every call on a device shares the
+ * array: each call rewrites all of the part it reads (nothing relies on earlier contents), and calls that OVERLAP on the
+ * GPU (different streams, or two host threads on one device without ordering) race on it -- serialise them. */
+#define AMAV_TC_STATIC_MAX_C 512
+int amav_triplane_project_tc_static(int F, int C, int R, const float *tokens, int64_t token_frame_stride,
+                                    const float *weight, float *proj, void *stream);
+
 /* Same projection from the producer's own layout: tokens_tm [F, 3*R*R, C] token-major, i.e. the upstream
  * transformer's hidden_states before its `.permute(0, 2, 1).contiguous()` (src/models/transformers.py:1070-1073; the
  * residual it adds afterwards is added in the same layout).  Texel (p, t) of frame f is the C contiguous floats at
