@@ -14,6 +14,10 @@
 // HBM traffic: D*(8 w + 8 r + 4 w) instead of D*12*2*passes.
 #include "common.cuh"
 
+#ifndef AMAV_SORT_GROUPS
+#define AMAV_SORT_GROUPS 1          // 1: grouped small-bucket sort (sort_groups); 0: one tile at a time (sort_tiles<256, 4096>)
+#endif
+
 namespace {
 
 constexpr int SCAN_THREADS = 256;
@@ -496,6 +500,185 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Grouped small-bucket sort.  The buckets of consecutive tiles are adjacent in `entries` (tile_start is a scan), so a
+// CTA sorts a GROUP of consecutive tiles whose buckets add up to <= CAP entries in ONE pass of the depth-bin sort: the
+// barriers, the bin scan and the queue pop are paid once per ~CAP entries instead of once per tile (mean bucket: 665
+// entries at 1024^2, a fifth of the tiles non-empty), every thread has CAP / T entries in flight per phase, and tiny
+// buckets ride along with their neighbours.  Tile j of the group owns the bins [start_j - start_group, +n_j) -- as many
+// bins as entries -- and maps its depths linearly between its own min and max; one scan over the group's bins then
+// gives every entry's bin its final range in the group, and the rank among the (about one) entries of the bin on the
+// full 64-bit (depth bits, Gaussian) key finishes the order.  Entries stay in registers from the global load to the
+// scatter; the slot inside the bin is the return value of the counting atomic (no second atomic pass).
+// A group with a bin fuller than SORT_MAX_BIN (depths too clustered) is redone tile by tile on the bitonic network.
+constexpr int GRP_T = 256, GRP_CAP = 4096, GRP_POP = 32, GRP_PER = GRP_CAP / GRP_T;
+
+__global__ void __launch_bounds__(GRP_T, 4) sort_groups(unsigned int num_tiles_total, const uint32_t *__restrict__ tile_start,
+                                                        const uint64_t *__restrict__ entries,
+                                                        int32_t *__restrict__ point_list, int64_t capacity,
+                                                        unsigned int *work_counter)
+{
+    constexpr int T = GRP_T, CAP = GRP_CAP, POP = GRP_POP, PER = GRP_PER;
+    extern __shared__ uint64_t s_sort[];
+    uint64_t *s_ent = s_sort;                                            // [CAP]
+    uint32_t *s_bin = reinterpret_cast<uint32_t *>(s_sort + CAP);        // [CAP + T + 1]: counts, then exclusive starts
+    __shared__ unsigned int s_next;
+    __shared__ uint32_t s_ts[POP + 1];
+    __shared__ uint32_t s_lo[POP], s_hi[POP];
+    __shared__ float s_scale[POP];
+    __shared__ uint32_t s_wsum[T / 32];
+    __shared__ int s_bad;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_next = atomicAdd(work_counter, (unsigned int)POP);
+        __syncthreads();
+        const unsigned int t0 = s_next;
+        if (t0 >= num_tiles_total) break;
+        const int nt = (int)min((unsigned int)POP, num_tiles_total - t0);
+        if (tid <= nt) {
+            const int64_t v = tile_start[t0 + tid];
+            s_ts[tid] = (uint32_t)(v > capacity ? capacity : v);
+        }
+        __syncthreads();
+        int a = 0;
+        while (a < nt) {                                          // uniform: every thread forms the same groups
+            const uint32_t sa = s_ts[a];
+            int b = a + 1;
+            const uint32_t n0 = s_ts[b] - sa;
+            if (n0 == 0u || n0 > (uint32_t)CAP) { a = b; continue; }   // empty, or the large-bucket kernel's
+            while (b < nt && s_ts[b + 1] - sa <= (uint32_t)CAP) ++b;
+            const int n = (int)(s_ts[b] - sa);
+            const int ga = a;
+            a = b;
+            if (n == 1) {
+                if (tid == 0) point_list[sa] = (int32_t)(uint32_t)entries[sa];
+                continue;
+            }
+            const int slots = (n + T - 1) / T;                   // uniform
+            const int per = ((n + 1 + T - 1) / T) | 1;           // bins per thread in the scan (odd: conflict-free stride)
+            __syncthreads();                                     // the previous group is done with shared memory
+            uint64_t ent[PER];
+            uint32_t meta[PER];
+#pragma unroll
+            for (int k = 0; k < PER; ++k) {
+                if (k >= slots) break;
+                const int i = tid + k * T;
+                ent[k] = i < n ? entries[(int64_t)sa + i] : 0ull;
+            }
+            for (int i = tid; i < T * per; i += T) s_bin[i] = 0u;
+            if (tid < b - ga) { s_lo[ga + tid] = 0xffffffffu; s_hi[ga + tid] = 0u; }
+            if (tid == 0) s_bad = 0;
+            __syncthreads();
+            // tile of every entry (a forward walk: a thread's entries are T apart) and the tiles' depth ranges
+            {
+                int j = ga;
+#pragma unroll
+                for (int k = 0; k < PER; ++k) {
+                    if (k >= slots) break;
+                    const int i = tid + k * T;
+                    const bool valid = i < n;
+                    if (valid) {
+                        const uint32_t pos = sa + (uint32_t)i;
+                        while (pos >= s_ts[j + 1]) ++j;
+                    }
+                    const uint32_t d = (uint32_t)(ent[k] >> 32);
+                    const int j0 = __shfl_sync(0xffffffffu, j, 0);
+                    const bool v0 = __shfl_sync(0xffffffffu, (int)valid, 0) != 0;      // lane 0 holds the warp's lowest i
+                    if (v0) {
+                        if (__all_sync(0xffffffffu, !valid || j == j0)) {
+                            const uint32_t lo = __reduce_min_sync(0xffffffffu, valid ? d : 0xffffffffu);
+                            const uint32_t hi = __reduce_max_sync(0xffffffffu, valid ? d : 0u);
+                            if (lane == 0) { atomicMin(&s_lo[j0], lo); atomicMax(&s_hi[j0], hi); }
+                        } else if (valid) {
+                            atomicMin(&s_lo[j], d); atomicMax(&s_hi[j], d);
+                        }
+                    }
+                    meta[k] = (uint32_t)j;
+                }
+            }
+            __syncthreads();
+            if (tid < b - ga) {
+                const int j = ga + tid;
+                s_scale[j] = (float)(s_ts[j + 1] - s_ts[j]) / ((float)(s_hi[j] - s_lo[j]) + 1.0f);
+            }
+            __syncthreads();
+            // pass 1: bin of every entry; the counting atomic's return value is the entry's slot inside the bin
+#pragma unroll
+            for (int k = 0; k < PER; ++k) {
+                if (k >= slots) break;
+                const int i = tid + k * T;
+                if (i < n) {
+                    const int j = (int)meta[k];
+                    const uint32_t tsj = s_ts[j];
+                    const int nj = (int)(s_ts[j + 1] - tsj);
+                    const int bl = min(nj - 1, (int)((float)((uint32_t)(ent[k] >> 32) - s_lo[j]) * s_scale[j]));
+                    const uint32_t bin = (tsj - sa) + (uint32_t)bl;
+                    const uint32_t slot = atomicAdd(&s_bin[bin], 1u);
+                    meta[k] = bin | (slot << 13);
+                }
+            }
+            __syncthreads();
+            // exclusive scan of the n + 1 bin counts (`per` consecutive bins per thread; bins past n hold zero)
+            {
+                uint32_t sum = 0, mx = 0;
+                for (int q = 0; q < per; ++q) { const uint32_t c = s_bin[tid * per + q]; sum += c; mx = max(mx, c); }
+                if (mx > SORT_MAX_BIN) s_bad = 1;
+                const uint32_t inc = warp_inclusive_scan(sum);
+                if (lane == 31) s_wsum[warp] = inc;
+                __syncthreads();
+                uint32_t base = inc - sum;
+#pragma unroll
+                for (int w = 0; w < T / 32; ++w)
+                    if (w < warp) base += s_wsum[w];
+                for (int q = 0; q < per; ++q) {
+                    const uint32_t c = s_bin[tid * per + q];
+                    s_bin[tid * per + q] = base;
+                    base += c;
+                }
+            }
+            __syncthreads();
+            if (s_bad) {                                         // clustered depths: tile by tile on the bitonic network
+                for (int j = ga; j < b; ++j) {
+                    const uint32_t sj = s_ts[j];
+                    const int nj = (int)(s_ts[j + 1] - sj);
+                    if (nj == 0) continue;
+                    __syncthreads();
+                    for (int i = tid; i < nj; i += T) s_ent[i] = entries[(int64_t)sj + i];
+                    __syncthreads();
+                    if (nj > 1) bitonic_sort(s_ent, nj, max(1, 32 - __clz(nj - 1)));
+                    for (int i = tid; i < nj; i += T) point_list[(int64_t)sj + i] = (int32_t)(uint32_t)s_ent[i];
+                }
+                continue;
+            }
+            // pass 2: scatter into the bins
+#pragma unroll
+            for (int k = 0; k < PER; ++k) {
+                if (k >= slots) break;
+                const int i = tid + k * T;
+                if (i < n) s_ent[s_bin[meta[k] & 0x1fffu] + (meta[k] >> 13)] = ent[k];
+            }
+            __syncthreads();
+            // pass 3: final position = bin start + rank among the entries of the bin; the Gaussian index goes out
+            int32_t *out = point_list + (int64_t)sa;
+#pragma unroll
+            for (int k = 0; k < PER; ++k) {
+                if (k >= slots) break;
+                const int i = tid + k * T;
+                if (i < n) {
+                    const uint32_t bin = meta[k] & 0x1fffu;
+                    const int e0 = (int)s_bin[bin], e1 = (int)s_bin[bin + 1];
+                    int rank = e0;
+                    if (e1 - e0 > 1)
+                        for (int q = e0; q < e1; ++q) rank += s_ent[q] < ent[k];
+                    out[rank] = (int32_t)(uint32_t)ent[k];
+                }
+            }
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" int64_t amav_splat_scan_tmp_elems(int64_t num_tiles_total)
@@ -555,15 +738,25 @@ extern "C" int amav_splat_bin(const AmavSplatDims *d, const float *geom, const u
         tile_start, tile_cursor, entries, capacity, overflow, use_smem);
     AMAV_CHECK_LAUNCH();
     // small buckets: queue head = overflow[1]; large buckets: queue head = tile_cursor[0], free once the scatter is done
-    auto small = sort_tiles<SORT_SMALL_T, SORT_SMALL_CAP, SORT_SMALL_POP, 0, false>;
     auto large = sort_tiles<SORT_LARGE_T, SORT_LARGE_CAP, SORT_LARGE_POP, SORT_SMALL_CAP, true>;
-    const int64_t want = (nt + SORT_SMALL_POP - 1) / SORT_SMALL_POP;
-    const int grid = (int)(want < AMAV_SM_COUNT * 4 ? want : AMAV_SM_COUNT * 4);
-    const int small_smem = SORT_SMALL_CAP * 12, large_smem = SORT_LARGE_CAP * 12;
-    amav_ensure_dyn_smem((const void *)small, small_smem);
+    const int large_smem = SORT_LARGE_CAP * 12;
     amav_ensure_dyn_smem((const void *)large, large_smem);
-    small<<<grid, SORT_SMALL_T, small_smem, stream>>>((unsigned int)nt, tile_start, entries, point_list, capacity,
-                                                      reinterpret_cast<unsigned int *>(overflow) + 1);
+    unsigned int *small_queue = reinterpret_cast<unsigned int *>(overflow) + 1;
+#if AMAV_SORT_GROUPS
+    static_assert(GRP_CAP == SORT_SMALL_CAP, "the large-bucket kernel takes every bucket above the grouped sort's capacity");
+    const int64_t want = (nt + GRP_POP - 1) / GRP_POP;
+    const int small_smem = GRP_CAP * 8 + (GRP_CAP + GRP_T + 1) * 4;
+    amav_ensure_dyn_smem((const void *)sort_groups, small_smem);
+    sort_groups<<<(int)(want < AMAV_SM_COUNT * 4 ? want : AMAV_SM_COUNT * 4), GRP_T, small_smem, stream>>>(
+        (unsigned int)nt, tile_start, entries, point_list, capacity, small_queue);
+#else
+    auto small = sort_tiles<SORT_SMALL_T, SORT_SMALL_CAP, SORT_SMALL_POP, 0, false>;
+    const int64_t want = (nt + SORT_SMALL_POP - 1) / SORT_SMALL_POP;
+    const int small_smem = SORT_SMALL_CAP * 12;
+    amav_ensure_dyn_smem((const void *)small, small_smem);
+    small<<<(int)(want < AMAV_SM_COUNT * 4 ? want : AMAV_SM_COUNT * 4), SORT_SMALL_T, small_smem, stream>>>(
+        (unsigned int)nt, tile_start, entries, point_list, capacity, small_queue);
+#endif
     AMAV_CHECK_LAUNCH();
     if (cudaMemsetAsync(tile_cursor, 0, sizeof(uint32_t), stream) != cudaSuccess) {
         amav_set_error("%s: cudaMemsetAsync failed", __func__);
