@@ -14,6 +14,19 @@
 // HBM traffic: D*(8 w + 8 r + 4 w) instead of D*12*2*passes.
 #include "common.cuh"
 
+#ifndef AMAV_SCAT_CTAS
+#define AMAV_SCAT_CTAS 4            // resident scatter CTAs per SM (measured: 2, 3 and 4 time the same)
+#endif
+#ifndef AMAV_SCAT_CHUNK
+// Gaussians per scatter CTA.  512 keeps the frames in flight (resident CTAs / CTAs per frame: 2.3 at 100k Gaussians)
+// and their ~12 MB each of half-written bucket sectors inside the L2; at 2048 nine frames were in flight, partially
+// written sectors were evicted and the DRAM paid read-modify-writes: bin 2.20 -> 1.82 ms per 120 frames (1024: 2.05,
+// 256: 1.86), 6.30 -> 5.47 ms at 500k Gaussians / 2048^2.
+#define AMAV_SCAT_CHUNK 512
+#endif
+#ifndef AMAV_SCAT_LDCS
+#define AMAV_SCAT_LDCS 0            // 1: rectangle / depth loads with the evict-first hint
+#endif
 #ifndef AMAV_SORT_GROUPS
 #define AMAV_SORT_GROUPS 1          // 1: grouped small-bucket sort (sort_groups); 0: one tile at a time (sort_tiles<256, 4096>)
 #endif
@@ -149,10 +162,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t *__res
 //   C. every entry takes its slot with a shared-memory atomicAdd on that position and is written out.
 // The order inside a bucket is arbitrary (the per-tile sort fixes it).  ~20x fewer global atomics than one cursor
 // bump per entry.  use_smem == 0: direct global cursor per entry (more tiles than fit in shared memory).
-constexpr int SCAT_CHUNK = 2048;
+constexpr int SCAT_CHUNK = AMAV_SCAT_CHUNK;
 constexpr int SCAT_PER = SCAT_CHUNK / 256;
 
-__global__ void __launch_bounds__(256, 3) scatter_entries(int N, int gx, int tiles, const float4 *__restrict__ geom,
+__global__ void __launch_bounds__(256, AMAV_SCAT_CTAS) scatter_entries(int N, int gx, int tiles, const float4 *__restrict__ geom,
                                                         const ushort4 *__restrict__ rect,
                                                         const uint32_t *__restrict__ tile_start,
                                                         uint32_t *__restrict__ tile_cursor,
@@ -168,12 +181,25 @@ __global__ void __launch_bounds__(256, 3) scatter_entries(int N, int gx, int til
 #pragma unroll
     for (int k = 0; k < SCAT_PER; ++k) {
         const int i = blockIdx.x * SCAT_CHUNK + k * 256 + threadIdx.x;
+        #if AMAV_SCAT_LDCS
+        rc[k] = make_ushort4(0, 0, 0, 0);
+        if (i < N) {
+            const uint2 r2 = __ldcs(reinterpret_cast<const uint2 *>(rect) + (int64_t)f * N + i);
+            rc[k] = make_ushort4((unsigned short)(r2.x & 0xffffu), (unsigned short)(r2.x >> 16), (unsigned short)(r2.y & 0xffffu),
+                                 (unsigned short)(r2.y >> 16));
+        }
+#else
         rc[k] = i < N ? rect[(int64_t)f * N + i] : make_ushort4(0, 0, 0, 0);
+#endif
     }
 #pragma unroll
     for (int k = 0; k < SCAT_PER; ++k) {
         const int i = blockIdx.x * SCAT_CHUNK + k * 256 + threadIdx.x;
+        #if AMAV_SCAT_LDCS
+        depth[k] = (rc[k].z > rc[k].x && rc[k].w > rc[k].y) ? __ldcs(reinterpret_cast<const float *>(geom + 3 * ((int64_t)f * N + i) + 2) + 2) : 0.0f;
+#else
         depth[k] = (rc[k].z > rc[k].x && rc[k].w > rc[k].y) ? geom[3 * ((int64_t)f * N + i) + 2].z : 0.0f;
+#endif
     }
     if (use_smem) {
         for (int t = threadIdx.x; t < tiles; t += 256) s_pos[t] = 0u;

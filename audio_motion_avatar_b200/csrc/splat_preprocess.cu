@@ -26,7 +26,10 @@ struct PreprocessParams {
 // one global atomicAdd per non-empty (CTA, tile): ~20x fewer global atomics than one per (Gaussian, tile) -- the
 // body covers a few hundred tiles, a chunk emits ~16k entries.  `use_smem == 0` (more tiles than fit in shared
 // memory) falls back to direct global atomics.
-constexpr int PRE_CHUNK = 2048;
+#ifndef AMAV_PRE_CHUNK
+#define AMAV_PRE_CHUNK 2048
+#endif
+constexpr int PRE_CHUNK = AMAV_PRE_CHUNK;
 
 __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessParams p, const int use_smem)
 {
