@@ -538,7 +538,10 @@ __global__ void __launch_bounds__(T, T == 256 ? 4 : 1) sort_tiles(unsigned int n
 // full 64-bit (depth bits, Gaussian) key finishes the order.  Entries stay in registers from the global load to the
 // scatter; the slot inside the bin is the return value of the counting atomic (no second atomic pass).
 // A group with a bin fuller than SORT_MAX_BIN (depths too clustered) is redone tile by tile on the bitonic network.
-constexpr int GRP_T = 256, GRP_CAP = 4096, GRP_POP = 32, GRP_PER = GRP_CAP / GRP_T;
+#ifndef AMAV_GRP_POP
+#define AMAV_GRP_POP 32
+#endif
+constexpr int GRP_T = 256, GRP_CAP = 4096, GRP_POP = AMAV_GRP_POP, GRP_PER = GRP_CAP / GRP_T;
 
 __global__ void __launch_bounds__(GRP_T, 4) sort_groups(unsigned int num_tiles_total, const uint32_t *__restrict__ tile_start,
                                                         const uint64_t *__restrict__ entries,

@@ -202,6 +202,69 @@ class PeerFrameGather:
         self.handle.barrier()
         return self.local if self.rank == self.dst else None
 
+    def enable_u8(self) -> None:
+        """Allocate the uint8 destination buffer (symmetric memory: a collective call, every rank makes it)."""
+        if getattr(self, "local_u8", None) is None:
+            import torch.distributed._symmetric_memory as symm
+            self.local_u8 = symm.empty(self.shape, dtype=torch.uint8, device=self.local.device)
+            self.handle_u8 = symm.rendezvous(self.local_u8, self.group)
+            self.target_u8 = self.handle_u8.get_buffer(self.dst, self.shape, torch.uint8)
+
+    def render_staged_u8(self, render, tokens: torch.Tensor, cams: dict, params: dict, chunks: int = 4,
+                         bgr: bool = False) -> Optional[torch.Tensor]:
+        """``render_staged`` for a consumer that wants 8-bit frames (the demo's video sink, main2.py:226-239,332-363:
+        ``(frame * 255).astype(np.uint8)``, optionally RGB -> BGR): every piece is converted on the rank that rendered it
+        (amav_frames_to_u8) and only the uint8 frames cross NVLink -- 3.1 MB per 1024^2 frame into the destination instead
+        of 12.6 MB, which takes the destination's ingress (the limiter of the fp32 gather at 8 GPUs) off the critical
+        path.  Returns uint8 [num_frames, H, W, 3] on ``dst``, None elsewhere.  Opt-in: the fp32 gather stays the default."""
+        from .stages import frames_to_u8
+        self.enable_u8()
+        n = self.stop - self.start
+        if tokens.shape[1] != n:
+            raise ValueError(f"rank {self.rank} holds {tokens.shape[1]} frames, its shard has {n}")
+        dev = tokens.device
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(dev)
+            self._staging = [None, None]
+            self._staged_free = [None, None]
+        if getattr(self, "_staging_u8", None) is None:
+            self._staging_u8 = [None, None]
+            self._staged_u8_free = [None, None]
+        cuts = chunk_bounds(n, chunks)
+        piece = max((cuts[i + 1] - cuts[i] for i in range(len(cuts) - 1)), default=0)
+        if piece and (self._staging[0] is None or self._staging[0].shape[0] < piece):
+            self._staging[0] = torch.empty((piece,) + self.shape[1:], dtype=torch.float32, device=dev)
+        for k in range(len(cuts) - 1):
+            a, b = cuts[k], cuts[k + 1]
+            if b <= a:
+                continue
+            stage = self._staging[0][:b - a]                  # fp32 piece: consumed by the conversion on the same stream
+            with torch.no_grad():
+                render(tokens[:, a:b], {m: v[:, a:b] for m, v in cams.items()}, None, {m: v[:, a:b] for m, v in params.items()},
+                       out=stage)
+            if self.rank == self.dst:
+                frames_to_u8(stage, bgr=bgr, out=self.local_u8, out_first=self.start + a)
+                continue
+            slot = k & 1
+            if self._staging_u8[slot] is None or self._staging_u8[slot].shape[0] < piece:
+                self._staging_u8[slot] = torch.empty((piece,) + self.shape[1:], dtype=torch.uint8, device=dev)
+            if self._staged_u8_free[slot] is not None:
+                main.wait_event(self._staged_u8_free[slot])
+            st8 = self._staging_u8[slot][:b - a]
+            frames_to_u8(stage, bgr=bgr, out=st8)
+            done = torch.cuda.Event()
+            done.record(main)
+            with torch.cuda.stream(self._copy_stream):
+                self._copy_stream.wait_event(done)
+                self.target_u8[self.start + a:self.start + b].copy_(st8, non_blocking=True)
+                freed = torch.cuda.Event()
+                freed.record(self._copy_stream)
+            self._staged_u8_free[slot] = freed
+        main.wait_stream(self._copy_stream)
+        self.handle_u8.barrier()
+        return self.local_u8 if self.rank == self.dst else None
+
     def capture(self, renderer, tokens: torch.Tensor, cams: dict, params: dict):
         """CUDA-graph this rank's shard render with the peer stores inside the graph (``Renderer.capture`` with
         ``out`` = this rank's slice of the destination buffer).  A 15-frame shard (120 frames over 8 GPUs) is ~2 ms of

@@ -803,6 +803,29 @@ def run_ours(args):
         line["weak"] = {"value": world * Ftot / (wms * 1e-3), "unit": UNIT, "ms_per_step": wms, "frames_per_rank": Ftot,
                         "frames_total": world * Ftot, "scaling": "weak", "gather": wmode, "clocks": wclk,
                         "overflow": bool(wbox["chk"].overflowed())}
+        # opt-in 8-bit gather (the demo's video sink wants uint8): converted where rendered, 4x fewer bytes into rank 0;
+        # a separate line -- the fp32 gather above stays the headline
+        if wpeer is not None:
+            from audio_motion_avatar_b200.stages import frames_to_u8
+
+            def u8_step():
+                with deferred_overflow_checks() as chk:
+                    wpeer.render_staged_u8(r, wtok, wcam_d, wpar_d, chunks=max(1, wtok.shape[1] // 60), bgr=True)   # 94 MB per 30 frames: the copies need no fine pieces
+                wbox["chk8"] = chk
+            ums, uclk, _ = ctx.timed(u8_step, steps, warmup)
+            blk8 = {"value": world * Ftot / (ums * 1e-3), "unit": UNIT, "ms_per_step": ums, "frames_total": world * Ftot,
+                    "out": "uint8 BGR [F,H,W,3] on rank 0 (amav_frames_to_u8 on the rendering rank, staged peer copies)",
+                    "bytes_into_rank0": (world - 1) * Ftot * size * size * 3, "clocks": uclk,
+                    "overflow": bool(wbox["chk8"].overflowed())}
+            if rank == 0:                                # rank 1's first frame in the gathered buffer == a local render of it
+                tk1, pr1, cm1 = synthetic_inputs(Ftot, Ftot + 1, world * Ftot, size, dev)
+                with torch.no_grad():
+                    one, _ = r(tk1, {k: v.to(dev) for k, v in cm1.items()}, None, {k: v.to(dev) for k, v in pr1.items()})
+                torch.cuda.synchronize()
+                blk8["rank1_frame0_bit_exact"] = bool(torch.equal(wpeer.local_u8[Ftot], frames_to_u8(one[0], bgr=True)[0]))
+                del tk1, one
+            ctx.barrier()
+            line["weak"]["u8_gather"] = blk8
         del wtok, wpeer, wbuf
         torch.cuda.empty_cache()
 

@@ -55,6 +55,17 @@ def _worker(rank, world, port, q):
         dist.barrier()
         if rank == 0:
             ok = ok and out4 is not None and torch.equal(out4, full[0])
+        # uint8 gather (the demo's video sink): converted on the rendering rank, only the 8-bit frames cross NVLink
+        from audio_motion_avatar_b200.stages import frames_to_u8
+        want8 = frames_to_u8(full[0], bgr=True)
+        for _ in range(2):
+            out5 = peer.render_staged_u8(r, tk, cm, pr, chunks=2, bgr=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if rank == 0:
+            ok = ok and out5 is not None and out5.dtype == torch.uint8 and torch.equal(out5, want8)
+        else:
+            assert out5 is None
         # the same shard step as one CUDA graph with the peer stores inside (PeerFrameGather.capture)
         if rank == 0:
             peer.local.zero_()
