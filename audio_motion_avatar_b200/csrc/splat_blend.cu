@@ -26,10 +26,20 @@
 #ifndef AMAV_ROWS_BULK_STORE
 #define AMAV_ROWS_BULK_STORE 1
 #endif
+// 1: the staged batches are double-buffered: the records of batch b + 1 are fetched with cp.async while the warps walk
+// batch b (one CTA barrier per batch, the gather latency hidden behind the walk); 0: one buffer, two barriers per batch
+#ifndef AMAV_BLEND_DB
+#define AMAV_BLEND_DB 1
+#endif
 
 namespace {
 
 using namespace amav_blend;
+
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void *gptr)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" :: "r"(saddr), "l"(gptr) : "memory");
+}
 
 constexpr int FWD_THREADS = 128;         // 4 warps x (8 x 8 pixels), 2 pixels per thread
 constexpr int FWD_BATCH = 256;           // staged list entries per batch
@@ -58,7 +68,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
 {
     // one 48-byte record per staged entry: (x, y, -conic.x/2, -conic.y)(-conic.z/2, opacity, pmin, r)(g, b, depth, radius);
     // a single array so the list walk needs one address per entry (immediate offsets for the rest)
-    __shared__ float4 s_rec[FWD_BATCH * 3];
+    constexpr bool DB = AMAV_BLEND_DB && ROWS == 0;      // the row-store instantiations keep one buffer (their s_out needs the room)
+    __shared__ float4 s_rec[FWD_BATCH * 3 * (DB ? 2 : 1)];
     // per warp: shared addresses (record base + 48 j) of the batch entries that touch its block
     __shared__ __align__(4) unsigned short s_list[FWD_THREADS / 32][FWD_BATCH];
     __shared__ unsigned int s_next;
@@ -75,7 +86,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
     // not in a cluster starts at 0), so the list walk does no address arithmetic at all
     const uint32_t rec_base = (uint32_t)__cvta_generic_to_shared(s_rec);
     const uint32_t list_base = (uint32_t)__cvta_generic_to_shared(list);
-    if (rec_base + 48u * FWD_BATCH > 0x10000u) __trap();          // the lists hold 16-bit shared addresses
+    if (rec_base + 48u * FWD_BATCH * (DB ? 2 : 1) > 0x10000u) __trap();   // the lists hold 16-bit shared addresses
+    unsigned int bb = 0;                      // DB: batches whose copy has been issued so far (CTA-uniform): batch x lives in buffer x & 1
 
     // NEQ (local output, tile lists from the scan): the queue holds the NON-EMPTY tiles only (four in five are empty at
     // 1024^2: a pop, two barriers and a 3 KB store each); the empty ones get their background here, without the queue
@@ -165,10 +177,46 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
         float2 C0 = make_float2(0.0f, 0.0f), C1 = C0, C2 = C0, Dv = C0;
         int last0 = 0, last1 = 0;                  // 1-based list position of the pixel's last contributor (n_contrib)
         int todo = (int)(r1 - r0), before = 0;     // `before`: list entries in earlier batches
+        // DB: buffer x & 1 may be overwritten once every warp has passed the barrier at the top of batch x - 1 (they are
+        // done walking batch x - 2); the copy of batch x is issued right after that barrier, also across tile boundaries.
+        int gn0 = -1, gn1 = -1;                    // Gaussians of the next batch to copy (this thread's two records)
+        auto load_idx = [&](uint32_t bs, int left) {
+            const int nbn = left < FWD_BATCH ? left : FWD_BATCH;
+            gn0 = (int)threadIdx.x < nbn ? p.point_list[bs + threadIdx.x] : -1;
+            gn1 = (int)threadIdx.x + FWD_THREADS < nbn ? p.point_list[bs + threadIdx.x + FWD_THREADS] : -1;
+        };
+        auto issue = [&]() {
+            const uint32_t dst = rec_base + (bb & 1u) * (48u * FWD_BATCH) + 48u * threadIdx.x;
+            if (gn0 >= 0) {
+                const float4 *src = geom + 3 * (int64_t)gn0;
+                cp_async16(dst, src); cp_async16(dst + 16u, src + 1); cp_async16(dst + 32u, src + 2);
+            }
+            if (gn1 >= 0) {
+                const float4 *src = geom + 3 * (int64_t)gn1;
+                cp_async16(dst + 48u * FWD_THREADS, src); cp_async16(dst + 48u * FWD_THREADS + 16u, src + 1);
+                cp_async16(dst + 48u * FWD_THREADS + 32u, src + 2);
+            }
+            asm volatile("cp.async.commit_group;\n" ::: "memory");
+            ++bb;
+        };
+        if (DB && r0 < r1) {
+            load_idx(r0, todo);
+            issue();
+            if (r0 + FWD_BATCH < r1) load_idx(r0 + FWD_BATCH, todo - FWD_BATCH);
+        }
         for (uint32_t base = r0; base < r1; base += FWD_BATCH, todo -= FWD_BATCH, before += FWD_BATCH) {
+            if (DB) asm volatile("cp.async.wait_group 0;\n" ::: "memory");
             if (__syncthreads_count(T.x <= 0.0f && T.y <= 0.0f) == FWD_THREADS) break;
+            const uint32_t cur_par = DB ? (bb - 1u) & 1u : 0u;
+            const uint32_t cur_base = rec_base + cur_par * (48u * FWD_BATCH);
+            const float4 *rec_cur = s_rec + cur_par * (FWD_BATCH * 3);
             const int nb = todo < FWD_BATCH ? todo : FWD_BATCH;
-            {                                                    // stage: two records per thread, loads issued together
+            if (DB) {
+                if (base + FWD_BATCH < r1) {
+                    issue();
+                    if (base + 2 * FWD_BATCH < r1) load_idx(base + 2 * FWD_BATCH, todo - 2 * FWD_BATCH);
+                }
+            } else {                                             // stage: two records per thread, loads issued together
                 const int j0 = threadIdx.x, j1 = threadIdx.x + FWD_THREADS;
                 const int g0 = j0 < nb ? p.point_list[base + j0] : -1, g1 = j1 < nb ? p.point_list[base + j1] : -1;
                 float4 q0, q1, q2, q3, q4, q5;
@@ -176,16 +224,16 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
                 if (g1 >= 0) { const float4 *src = geom + 3 * (int64_t)g1; q3 = src[0]; q4 = src[1]; q5 = src[2]; }
                 if (g0 >= 0) { s_rec[3 * j0] = q0; s_rec[3 * j0 + 1] = q1; s_rec[3 * j0 + 2] = q2; }
                 if (g1 >= 0) { s_rec[3 * j1] = q3; s_rec[3 * j1 + 1] = q4; s_rec[3 * j1 + 2] = q5; }
+                __syncthreads();
             }
-            __syncthreads();
             if (__all_sync(0xffffffffu, T.x <= 0.0f && T.y <= 0.0f)) continue;
             // 1. this warp's list: batch entries whose footprint can reach its 8x8 block, in list order
             int cnt = 0;
             for (int j0 = 0; j0 < nb; j0 += 32) {
                 const int j = j0 + lane;
-                const bool keep = j < nb && warp_rect_keep<FWD_RW, FWD_RH>(s_rec[3 * j], s_rec[3 * j + 1], rx0, ry0);
+                const bool keep = j < nb && warp_rect_keep<FWD_RW, FWD_RH>(rec_cur[3 * j], rec_cur[3 * j + 1], rx0, ry0);
                 const unsigned int m = __ballot_sync(0xffffffffu, keep);
-                if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(rec_base + 48u * (uint32_t)j);
+                if (keep) list[cnt + __popc(m & ((1u << lane) - 1u))] = (unsigned short)(cur_base + 48u * (uint32_t)j);
                 cnt += __popc(m);
             }
             __syncwarp();
@@ -242,8 +290,8 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
 #pragma unroll 1
             for (; k < cnt; ++k) blend_entry(lds_u16<0>(list_base + 2u * (uint32_t)k));
             if (AUX) {
-                if (off0_last >= 0) last0 = before + (off0_last - (int)rec_base) / 48 + 1;
-                if (off1_last >= 0) last1 = before + (off1_last - (int)rec_base) / 48 + 1;
+                if (off0_last >= 0) last0 = before + (off0_last - (int)cur_base) / 48 + 1;
+                if (off1_last >= 0) last1 = before + (off1_last - (int)cur_base) / 48 + 1;
             }
         }
         // colour epilogue.  ROWS: HWC tile pairs go through shared memory and leave as 16 rows of 384 contiguous bytes
@@ -337,11 +385,6 @@ __global__ void __launch_bounds__(FWD_THREADS, 8) blend_kernel(const BlendParams
 constexpr int WK_THREADS = 128;
 constexpr int WK_WARPS = WK_THREADS / 32;
 constexpr int WK_CHUNK = 64;             // list entries per stage
-
-__device__ __forceinline__ void cp_async16(uint32_t saddr, const void *gptr)
-{
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(saddr), "l"(gptr) : "memory");
-}
 
 template <bool AUX>
 __global__ void __launch_bounds__(WK_THREADS, 8) blend_warp_kernel(const BlendParams p, const float *__restrict__ bg)
