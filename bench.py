@@ -789,6 +789,16 @@ def run_ours(args):
                                     "max_abs": float((got - ref).abs().max().item())}
             del tk, ref
         ctx.barrier()
+        # the same strong split with the opt-in 8-bit gather (a separate line; fp32 above is the headline): what the step
+        # costs once rank 0's ingress carries 3 bytes per pixel instead of 12
+        if peer is not None and want("weak"):
+            def s8_step():
+                with deferred_overflow_checks() as chk:
+                    peer.render_staged_u8(r, tokens, cams_d, params_d, chunks=1, bgr=True)
+                box["chk8"] = chk
+            s8ms, _, _ = ctx.timed(s8_step, steps, warmup, clocks=False)
+            line["u8_gather"] = {"value": Ftot / (s8ms * 1e-3), "unit": UNIT, "ms_per_step": s8ms, "frames_total": Ftot,
+                                 "out": "uint8 BGR [F,H,W,3] on rank 0", "overflow": bool(box["chk8"].overflowed())}
     del peer, gather_buf
     torch.cuda.empty_cache()
 
