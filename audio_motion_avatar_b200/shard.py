@@ -210,7 +210,7 @@ class PeerFrameGather:
             self.handle_u8 = symm.rendezvous(self.local_u8, self.group)
             self.target_u8 = self.handle_u8.get_buffer(self.dst, self.shape, torch.uint8)
 
-    def render_staged_u8(self, render, tokens: torch.Tensor, cams: dict, params: dict, chunks: int = 4,
+    def render_staged_u8(self, render, tokens: torch.Tensor, cams: dict, params: dict, chunks=4,
                          bgr: bool = False) -> Optional[torch.Tensor]:
         """``render_staged`` for a consumer that wants 8-bit frames (the demo's video sink, main2.py:226-239,332-363:
         ``(frame * 255).astype(np.uint8)``, optionally RGB -> BGR): every piece is converted on the rank that rendered it
@@ -231,7 +231,16 @@ class PeerFrameGather:
         if getattr(self, "_staging_u8", None) is None:
             self._staging_u8 = [None, None]
             self._staged_u8_free = [None, None]
-        cuts = chunk_bounds(n, chunks)
+        # ``chunks``: a number of equal pieces, or "halving": n/2, n/4, ... frames -- the render is the bottleneck of this
+        # variant, so only the LAST piece's copy is exposed and it should be the smallest
+        if chunks == "halving":
+            cuts, left = [0], n
+            while left > 16 and len(cuts) < 4:
+                cuts.append(cuts[-1] + left // 2)
+                left -= left // 2
+            cuts.append(n)
+        else:
+            cuts = chunk_bounds(n, chunks)
         piece = max((cuts[i + 1] - cuts[i] for i in range(len(cuts) - 1)), default=0)
         if piece and (self._staging[0] is None or self._staging[0].shape[0] < piece):
             self._staging[0] = torch.empty((piece,) + self.shape[1:], dtype=torch.float32, device=dev)

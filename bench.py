@@ -820,7 +820,7 @@ def run_ours(args):
 
             def u8_step():
                 with deferred_overflow_checks() as chk:
-                    wpeer.render_staged_u8(r, wtok, wcam_d, wpar_d, chunks=max(1, wtok.shape[1] // 60), bgr=True)   # 94 MB per 30 frames: the copies need no fine pieces
+                    wpeer.render_staged_u8(r, wtok, wcam_d, wpar_d, chunks="halving" if world >= 8 else max(1, wtok.shape[1] // 60), bgr=True)   # only the last piece's copy is exposed
                 wbox["chk8"] = chk
             ums, uclk, _ = ctx.timed(u8_step, steps, warmup)
             blk8 = {"value": world * Ftot / (ums * 1e-3), "unit": UNIT, "ms_per_step": ums, "frames_total": world * Ftot,

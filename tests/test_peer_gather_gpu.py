@@ -58,8 +58,8 @@ def _worker(rank, world, port, q):
         # uint8 gather (the demo's video sink): converted on the rendering rank, only the 8-bit frames cross NVLink
         from audio_motion_avatar_b200.stages import frames_to_u8
         want8 = frames_to_u8(full[0], bgr=True)
-        for _ in range(2):
-            out5 = peer.render_staged_u8(r, tk, cm, pr, chunks=2, bgr=True)
+        for ch in (2, "halving"):
+            out5 = peer.render_staged_u8(r, tk, cm, pr, chunks=ch, bgr=True)
         torch.cuda.synchronize()
         dist.barrier()
         if rank == 0:
