@@ -35,7 +35,15 @@ struct BlendBwdParams {
 
 constexpr int ACC_LD = 9;            // row stride of the smem accumulator (odd: conflict-free flush)
 constexpr int BW_THREADS = 128;      // 4 warps x (8 x 8 pixels): two pixels per thread, as in the forward kernel
-constexpr int BW_BATCH = 256;        // staged list entries per batch
+#ifndef AMAV_BW_BATCH
+#define AMAV_BW_BATCH 256
+#endif
+#ifndef AMAV_BW_CTAS
+#define AMAV_BW_CTAS 4
+#endif
+constexpr int BW_BATCH = AMAV_BW_BATCH;   // staged list entries per batch (128 < BW_BATCH <= 256: two records per thread)
+constexpr int BW_CTAS = AMAV_BW_CTAS;     // resident CTAs per SM the kernel is compiled for
+static_assert(BW_BATCH > 128 && BW_BATCH <= 256 && BW_BATCH % 4 == 0, "batch size");
 constexpr int BW_RW = 8, BW_RH = 8;
 
 // Round-2 shape: every thread owns TWO pixels of one column (rows ly, ly + 4), so the per-pair arithmetic runs on packed
@@ -45,7 +53,7 @@ constexpr int BW_RW = 8, BW_RH = 8;
 // folds the pending pair in one step earlier and then multiplies by exactly 1, so accum, T and every later term come out
 // bit-identical to skipping the pair -- and the walk needs no per-pixel select on its state (last_colour becomes the
 // previous entry's colour for the whole warp: a broadcast operand).
-__global__ void __launch_bounds__(BW_THREADS, 4) blend_bwd_kernel(const BlendBwdParams p, const float *__restrict__ bg)
+__global__ void __launch_bounds__(BW_THREADS, BW_CTAS) blend_bwd_kernel(const BlendBwdParams p, const float *__restrict__ bg)
 {
     // double-buffered batch state: thread t stages records t and t + 128 of a batch, zeroes their accumulator rows and
     // later flushes them, so consecutive batches need ONE barrier between them (after staging); the flush of batch k
@@ -117,7 +125,7 @@ __global__ void __launch_bounds__(BW_THREADS, 4) blend_bwd_kernel(const BlendBwd
         // flush of one staged batch: one record per (tile, Gaussian)
         auto flush = [&](int buf, int count) {
 #pragma unroll
-            for (int r = 0; r < BW_BATCH / BW_THREADS; ++r) {
+            for (int r = 0; r < (BW_BATCH + BW_THREADS - 1) / BW_THREADS; ++r) {
                 const int row = threadIdx.x + r * BW_THREADS;
                 if (row < count) {
                     const float *sa = s_accb[buf] + row * ACC_LD;
@@ -136,7 +144,7 @@ __global__ void __launch_bounds__(BW_THREADS, 4) blend_bwd_kernel(const BlendBwd
             }
         };
         int prev_nb = 0, it = 0;
-        for (int b = (nproc - 1) >> 8; b >= 0 && nproc > 0; --b, ++it) {
+        for (int b = (nproc - 1) / BW_BATCH; b >= 0 && nproc > 0; --b, ++it) {
             const int before = b * BW_BATCH;
             const int nb = min(BW_BATCH, nproc - before);
             const int buf = it & 1;
@@ -152,7 +160,10 @@ __global__ void __launch_bounds__(BW_THREADS, 4) blend_bwd_kernel(const BlendBwd
                 if (ga >= 0) { s_rec[3 * j0] = q0; s_rec[3 * j0 + 1] = q1; s_rec[3 * j0 + 2] = q2; s_gidb[buf][j0] = ga; }
                 if (gb >= 0) { s_rec[3 * j1] = q3; s_rec[3 * j1 + 1] = q4; s_rec[3 * j1 + 2] = q5; s_gidb[buf][j1] = gb; }
 #pragma unroll
-                for (int k = 0; k < ACC_LD; ++k) { s_acc[j0 * ACC_LD + k] = 0.0f; s_acc[j1 * ACC_LD + k] = 0.0f; }
+                for (int k = 0; k < ACC_LD; ++k) {
+                    s_acc[j0 * ACC_LD + k] = 0.0f;
+                    if (j1 < BW_BATCH) s_acc[j1 * ACC_LD + k] = 0.0f;
+                }
             }
             __syncthreads();                                   // batch staged; every warp has finished the previous batch
             flush(buf ^ 1, prev_nb);
@@ -318,7 +329,7 @@ extern "C" int amav_splat_blend_backward(const AmavSplatDims *d, const float *ge
     p.capacity = capacity > 0xffffffffll ? 0xffffffffu : (uint32_t)capacity;
     const int64_t total_tiles = (int64_t)d->frames * p.gx * p.gy;
     AMAV_CHECK_ARG(total_tiles < ((int64_t)1 << 31), "too many tiles");
-    const int grid = (int)(total_tiles < AMAV_SM_COUNT * 4 ? total_tiles : AMAV_SM_COUNT * 4);
+    const int grid = (int)(total_tiles < AMAV_SM_COUNT * BW_CTAS ? total_tiles : AMAV_SM_COUNT * BW_CTAS);
     blend_bwd_kernel<<<grid, BW_THREADS, 0, (cudaStream_t)stream>>>(p, bg);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
