@@ -48,11 +48,13 @@ project_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame_st
     const int kper = C / PJ_KGROUPS;
     const int c0 = warp * kper;
     const float *src = tokens + (int64_t)f * frame_stride + (int64_t)c0 * (3 * R2) + (int64_t)p * R2 + tile * PJ_TEX + lane * 4;
-    float acc[4][14];
+    // packed FP32 (sm_100 FFMA2): one instruction per (texel pair, output); each half is an IEEE fma, so the bits are
+    // those of the scalar loop
+    float2 acc[2][14];
 #pragma unroll
-    for (int t = 0; t < 4; ++t)
+    for (int t = 0; t < 2; ++t)
 #pragma unroll
-        for (int o = 0; o < 14; ++o) acc[t][o] = 0.0f;
+        for (int o = 0; o < 14; ++o) acc[t][o] = make_float2(0.0f, 0.0f);
 
     constexpr int U = 8;
     for (int cb = 0; cb < kper; cb += U) {
@@ -65,18 +67,20 @@ project_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame_st
             const float4 *wp = reinterpret_cast<const float4 *>(s_w + (size_t)(c0 + cb + u) * 16);
             const float4 w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
             const float w[14] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y, w2.z, w3.x, w3.y, w3.z};
-            const float tv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            const float2 t01 = make_float2(v[u].x, v[u].y), t23 = make_float2(v[u].z, v[u].w);
 #pragma unroll
-            for (int t = 0; t < 4; ++t)
-#pragma unroll
-                for (int o = 0; o < 14; ++o) acc[t][o] = fmaf(tv[t], w[o], acc[t][o]);
+            for (int o = 0; o < 14; ++o) {
+                const float2 ww = make_float2(w[o], w[o]);
+                acc[0][o] = __ffma2_rn(t01, ww, acc[0][o]);
+                acc[1][o] = __ffma2_rn(t23, ww, acc[1][o]);
+            }
         }
     }
     // cross-warp (K slice) reduction through shared memory: red[warp][o][texel]
 #pragma unroll
     for (int o = 0; o < 14; ++o)
         *reinterpret_cast<float4 *>(s_red + ((size_t)warp * 14 + o) * PJ_TEX + lane * 4) =
-            make_float4(acc[0][o], acc[1][o], acc[2][o], acc[3][o]);
+            make_float4(acc[0][o].x, acc[0][o].y, acc[1][o].x, acc[1][o].y);
     __syncthreads();
     // thread -> (texel, half of the 14 outputs)
     const int tex = threadIdx.x & (PJ_TEX - 1), half = threadIdx.x >> 7;
