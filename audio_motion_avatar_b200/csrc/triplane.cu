@@ -26,16 +26,16 @@ constexpr int PJ_KGROUPS = 8;          // one warp per K slice
 
 // smem: w[C][16] (slot-major per channel) then, after the main loop, red[8][128][16] reuses/extends it
 __global__ void __launch_bounds__(PJ_THREADS, 2)
-project_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame_stride,
+project_kernel(int F, int C, int R2, const float *__restrict__ tokens, int64_t frame_stride,
                const float *__restrict__ weight, int ldw, float *__restrict__ proj)
 {
     extern __shared__ float4 s_dyn[];
     float *s_w = reinterpret_cast<float *>(s_dyn);                   // [C][16]
     float *s_red = s_w + (size_t)C * 16;                             // [8][14][128]
+    // persistent CTAs: blockIdx.y = plane (its decoder columns stay in shared memory), blockIdx.x strides over the
+    // (frame, 128-texel tile) items of that plane
     const int tiles_per_plane = R2 / PJ_TEX;
-    const int tile = blockIdx.x % tiles_per_plane;
-    const int p = (blockIdx.x / tiles_per_plane) % 3;
-    const int f = blockIdx.x / (3 * tiles_per_plane);
+    const int p = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     for (int i = threadIdx.x; i < C * 16; i += PJ_THREADS) {
@@ -47,6 +47,8 @@ project_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame_st
 
     const int kper = C / PJ_KGROUPS;
     const int c0 = warp * kper;
+    for (int item = blockIdx.x; item < F * tiles_per_plane; item += gridDim.x) {
+    const int f = item / tiles_per_plane, tile = item - f * tiles_per_plane;
     const float *src = tokens + (int64_t)f * frame_stride + (int64_t)c0 * (3 * R2) + (int64_t)p * R2 + tile * PJ_TEX + lane * 4;
     // packed FP32 (sm_100 FFMA2): one instruction per (texel pair, output); each half is an IEEE fma, so the bits are
     // those of the scalar loop
@@ -100,6 +102,8 @@ project_kernel(int C, int R2, const float *__restrict__ tokens, int64_t frame_st
         out[7] = r[0];
         reinterpret_cast<float4 *>(out)[2] = make_float4(r[1], r[2], r[3], 0.0f);
         reinterpret_cast<float4 *>(out)[3] = make_float4(r[4], r[5], r[6], 0.0f);
+    }
+    __syncthreads();                                     // s_red is free for the next item
     }
 }
 
@@ -220,10 +224,11 @@ extern "C" int amav_triplane_project(int F, int C, int R, const float *tokens, i
     const size_t smem = ((size_t)C * 16 + (size_t)PJ_KGROUPS * 14 * PJ_TEX) * sizeof(float);
     AMAV_CHECK_ARG(smem <= 113 * 1024, "C too large for the shared-memory weight tile");
     amav_ensure_dyn_smem((const void *)project_kernel, (int)smem);
-    const int64_t grid = (int64_t)F * 3 * (R * R / PJ_TEX);
-    AMAV_CHECK_ARG(grid < ((int64_t)1 << 31), "too many tiles");
-    project_kernel<<<(unsigned)grid, PJ_THREADS, smem, (cudaStream_t)stream>>>(C, R * R, tokens, token_frame_stride,
-                                                                               weight, 3 + 3 * C, proj);
+    const int64_t items = (int64_t)F * (R * R / PJ_TEX);                 // per plane
+    AMAV_CHECK_ARG(items < ((int64_t)1 << 31), "too many tiles");
+    const int per_plane = (2 * AMAV_SM_COUNT) / 3;                        // 98 x 3 planes = 294 of the 296 resident CTAs
+    project_kernel<<<dim3((unsigned)(items < per_plane ? items : per_plane), 3), PJ_THREADS, smem, (cudaStream_t)stream>>>(
+        F, C, R * R, tokens, token_frame_stride, weight, 3 + 3 * C, proj);
     AMAV_CHECK_LAUNCH();
     return AMAV_OK;
 }
