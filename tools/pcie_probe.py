@@ -1,44 +1,23 @@
-"""Host<->device copy bandwidth of the box (pinned memory), alone and both directions at once: the ceiling of bench.py's
-e2e number (3.02 GB in + 1.51 GB out per 120-frame step)."""
-import time
+"""Host<->device copy rates of the box (pinned memory, CUDA events): what bounds the e2e line of bench.py."""
 import torch
-
-n = 1 << 30
-h_in = torch.empty(n, dtype=torch.uint8, pin_memory=True)
-h_out = torch.empty(n, dtype=torch.uint8, pin_memory=True)
-d_in = torch.empty(n, dtype=torch.uint8, device="cuda")
-d_out = torch.empty(n, dtype=torch.uint8, device="cuda")
-s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
-
-
-def timeit(fn, reps=5):
-    fn(); torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(reps):
-        fn()
+dev = torch.device("cuda", 0)
+def rate(nbytes, d2h=False, both=False, reps=10):
+    h = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True); d = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    h2 = torch.empty(nbytes // 2, dtype=torch.uint8, pin_memory=True); d2 = torch.empty(nbytes // 2, dtype=torch.uint8, device=dev)
+    s2 = torch.cuda.Stream(dev)
+    for _ in range(2):
+        d.copy_(h, non_blocking=True)
     torch.cuda.synchronize()
-    return (time.perf_counter() - t0) / reps
-
-
-def h2d():
-    with torch.cuda.stream(s1):
-        d_in.copy_(h_in, non_blocking=True)
-
-
-def d2h():
-    with torch.cuda.stream(s2):
-        h_out.copy_(d_out, non_blocking=True)
-
-
-def both():
-    h2d(); d2h()
-
-
-print("H2D GB/s", n / timeit(h2d) / 1e9)
-print("D2H GB/s", n / timeit(d2h) / 1e9)
-t = timeit(both)
-print("both: H2D+D2H GB/s each", n / t / 1e9)
-import subprocess
-print(subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True).stdout[:1500])
-import os
-print("cpus", os.cpu_count(), "affinity", len(os.sched_getaffinity(0)))
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        if d2h: h.copy_(d, non_blocking=True)
+        else: d.copy_(h, non_blocking=True)
+        if both:
+            with torch.cuda.stream(s2):
+                h2.copy_(d2, non_blocking=True)
+    b.record(); torch.cuda.synchronize(); s2.synchronize()
+    return nbytes * reps / (a.elapsed_time(b) * 1e-3) / 1e9
+for mb in (25, 100, 400, 1600):
+    n = mb << 20
+    print(f"{mb:5d} MB  H2D {rate(n):6.1f} GB/s   D2H {rate(n, d2h=True):6.1f} GB/s   H2D with concurrent D2H of half the size {rate(n, both=True):6.1f} GB/s")
