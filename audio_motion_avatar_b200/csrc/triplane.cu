@@ -131,7 +131,10 @@ __device__ __forceinline__ void tap_coords(float g, int R, int &i0, float &w1)
     w1 = i - fl;
 }
 
-__global__ void __launch_bounds__(256) sample_decode_kernel(const SampleParams p)
+#ifndef AMAV_SD_CTAS
+#define AMAV_SD_CTAS 6            // 40 registers, 48 warps per SM: the kernel is latency-bound (0.93 -> 0.88 ms; 8 CTAs spill: 0.92)
+#endif
+__global__ void __launch_bounds__(256, AMAV_SD_CTAS) sample_decode_kernel(const SampleParams p)
 {
     // per slot: (w_x, w_y, w_z, bias) of the decoder's xyz columns / bias
     __shared__ float4 s_wb[16];
