@@ -271,6 +271,10 @@ __global__ void __launch_bounds__(256) skin_kernel(int V, int J, const float *__
 // sites[f][i] = sum_k wgt[i][k] * verts[f][par[i][k]].  A thread keeps its site's table row in registers for DEN_FB
 // frames (P == 4, the level-2 table: one int4 + one float4 load); the sums run in the same order as one frame at a time.
 constexpr int DEN_FB = 8;
+#ifndef AMAV_DEN_UNROLL
+#define AMAV_DEN_UNROLL 1
+#endif
+constexpr int DEN_UNROLL = AMAV_DEN_UNROLL;      // frames of a thread's loop whose 12 gathers are issued together
 
 __global__ void __launch_bounds__(256) densify_kernel(int F, int V, int N, int P, const float *__restrict__ verts,
                                                        const int32_t *__restrict__ par, const float *__restrict__ wgt,
@@ -286,6 +290,7 @@ __global__ void __launch_bounds__(256) densify_kernel(int F, int V, int N, int P
         const float4 w = __ldg(reinterpret_cast<const float4 *>(wgt) + i);
         const int qq[4] = {q.x, q.y, q.z, q.w};
         const float ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll DEN_UNROLL
         for (int f = f0; f < f1; ++f) {
             const float *vb = verts + (int64_t)f * V * 3;
             float x = 0.0f, y = 0.0f, z = 0.0f;
