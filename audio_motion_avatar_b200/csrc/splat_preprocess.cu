@@ -31,7 +31,10 @@ struct PreprocessParams {
 #endif
 constexpr int PRE_CHUNK = AMAV_PRE_CHUNK;
 
-__global__ void __launch_bounds__(256) preprocess_kernel(const PreprocessParams p, const int use_smem)
+#ifndef AMAV_PRE_CTAS
+#define AMAV_PRE_CTAS 4
+#endif
+__global__ void __launch_bounds__(256, AMAV_PRE_CTAS) preprocess_kernel(const PreprocessParams p, const int use_smem)
 {
     extern __shared__ uint32_t s_hist[];
     const int f = blockIdx.y;
