@@ -56,6 +56,17 @@ def chunk_bounds(size: int, chunks: int) -> List[int]:
     return [(i * size + chunks - 1) // chunks for i in range(chunks + 1)]
 
 
+def halving_bounds(size: int, min_piece: int = 16, max_pieces: int = 4) -> List[int]:
+    """Piece boundaries size/2, size/4, ... for a pipeline whose LAST piece is the exposed one (render-bound staged
+    gathers): 120 -> [0, 60, 90, 105, 120]; at most ``max_pieces`` pieces, none cut below ``min_piece`` frames."""
+    cuts, left = [0], int(size)
+    while left > min_piece and len(cuts) < max_pieces:
+        cuts.append(cuts[-1] + left // 2)
+        left -= left // 2
+    cuts.append(int(size))
+    return cuts
+
+
 def render_and_gather(render, tokens: torch.Tensor, cams: dict, params: dict, num_frames: int, chunks: int = 4,
                       dst: int = 0, group=None, out: Optional[torch.Tensor] = None,
                       defer=None) -> Optional[torch.Tensor]:
@@ -233,14 +244,7 @@ class PeerFrameGather:
             self._staged_u8_free = [None, None]
         # ``chunks``: a number of equal pieces, or "halving": n/2, n/4, ... frames -- the render is the bottleneck of this
         # variant, so only the LAST piece's copy is exposed and it should be the smallest
-        if chunks == "halving":
-            cuts, left = [0], n
-            while left > 16 and len(cuts) < 4:
-                cuts.append(cuts[-1] + left // 2)
-                left -= left // 2
-            cuts.append(n)
-        else:
-            cuts = chunk_bounds(n, chunks)
+        cuts = halving_bounds(n) if chunks == "halving" else chunk_bounds(n, chunks)
         piece = max((cuts[i + 1] - cuts[i] for i in range(len(cuts) - 1)), default=0)
         if piece and (self._staging[0] is None or self._staging[0].shape[0] < piece):
             self._staging[0] = torch.empty((piece,) + self.shape[1:], dtype=torch.float32, device=dev)

@@ -93,3 +93,17 @@ def test_strong_split_frames_are_the_same_sequence():
             part = {k: v[:, f0:f1] for k, v in S.make_pose_sequence(1, 120, seed=0).items()}
             assert all(torch.equal(part[k], whole[k][:, f0:f1]) for k in whole)
     assert sum(frame_shard(120, r, 8)[1] - frame_shard(120, r, 8)[0] for r in range(8)) == 120
+
+
+def test_halving_piece_schedule_covers_the_shard_once():
+    """shard.halving_bounds: the piece schedule of the uint8 staged gather -- increasing bounds from 0 to n, pieces shrink,
+    the last piece is the smallest, no empty piece except for an empty shard."""
+    from audio_motion_avatar_b200.shard import halving_bounds
+    assert halving_bounds(120) == [0, 60, 90, 105, 120]
+    assert halving_bounds(60) == [0, 30, 45, 60]
+    for n in (0, 1, 2, 15, 16, 17, 33, 225, 1800):
+        cuts = halving_bounds(n)
+        assert cuts[0] == 0 and cuts[-1] == n and len(cuts) <= 5
+        pieces = [b - a for a, b in zip(cuts[:-1], cuts[1:])]
+        assert sum(pieces) == n and (n == 0 or all(p > 0 for p in pieces))
+        assert pieces == sorted(pieces, reverse=True) or pieces[-1] - pieces[-2] <= 1      # non-increasing up to the odd remainder
