@@ -7,8 +7,9 @@
 //   2. exclusive scan of tile_count (warp-shuffle scan, 3 small launches) -> tile_start = the
 //      upstream `ranges`, plus D at tile_start[last];
 //   3. scatter: every (Gaussian, tile) pair drops (depth_bits<<32 | gaussian) into its tile's bucket;
-//   4. one CTA per non-empty tile sorts its bucket in shared memory on the 64-bit entry
-//      (depth bits, then Gaussian index: unique keys) and writes the Gaussian indices.
+//   4. the buckets are sorted in shared memory on the 64-bit entry (depth bits, then Gaussian index: unique keys) and
+//      the Gaussian indices written out: groups of consecutive tiles of up to 4096 entries per pass of an O(n)
+//      depth-bin sort (sort_groups), larger buckets one at a time (sort_tiles<1024, 16384>).
 // The result equals the stable sort of upstream keys: within a tile ascending depth bits, ties in
 // ascending Gaussian index (upstream emits in index order and its radix sort is stable).
 // HBM traffic: D*(8 w + 8 r + 4 w) instead of D*12*2*passes.

@@ -13,8 +13,9 @@
 //   * the T recurrence is branch-free: a saturated pixel is marked by T <= 0 (its transmittance parked as -T), the
 //     weight of a rejected pair is selected to 0, so the list walk has no divergent branch and no flag;
 //   * persistent CTAs pull tiles from an atomic work counter, stage the tile's sorted records through shared memory
-//     in batches of 256, each warp culls the batch against its block (exact bound of the quadratic form) into a list
-//     of 16-bit shared addresses and walks the list two entries per iteration.
+//     in batches of 256 (double-buffered with cp.async in the local-output instantiations: batch b + 1 arrives while
+//     batch b is walked), each warp culls the batch against its block (exact bound of the quadratic form) into a list
+//     of 16-bit shared addresses and walks the list four entries per iteration.
 #include <stdlib.h>
 
 #include "blend_common.cuh"

@@ -3,8 +3,8 @@
 //
 // The decode is linear in the sampled features, so decode(bilinear(T)) == bilinear(decode(T)):
 //   1. triplane_project: every texel of every plane is pushed through the decoder heads once
-//      (a [R*R x C] . [C x 14] product per plane, fp32 FMA, HBM-bound: it reads the 25 MB/frame
-//      triplane exactly once and writes 0.8 MB/frame of 16-wide projected texels);
+//      (a [R*R x C] . [C x 14] product per plane, packed fp32 FMA, HBM-bound: it reads the 25 MB/frame
+//      triplane exactly once and writes 0.8 MB/frame of 16-wide projected texels; persistent CTAs per plane);
 //   2. sample_decode: per Gaussian site, 3 planes x 4 bilinear taps of 64-byte projected texels
 //      (L2-resident), the xyz/bias terms and construct_gaussians' activations.
 // The reference instead materialises [F,N,1536] sampled features (614 MB/frame) and reads them 5x.
