@@ -8,9 +8,10 @@
 // Upstream issues 9 global float atomicAdds per contributing (pixel, Gaussian) pair.  Here:
 //   * persistent CTAs pull tiles from a device queue (same imbalance as the forward);
 //   * a tile starts at the deepest list position any of its pixels reached (max n_contrib), not at the list end;
-//   * each warp owns an 8x4 pixel rectangle and culls every 256-entry batch against it (same exact bound as the
-//     forward), walks its list back to front, reduces the 9 per-pair terms over its 32 pixels with a 14-shuffle
-//     split butterfly, and adds them to a per-batch accumulator in shared memory;
+//   * each warp owns an 8x8 pixel block (two pixels per thread, packed FP32) and culls every 256-entry batch against
+//     it (same exact bound as the forward), walks its list back to front in groups of four entries, reduces the
+//     4 x 9 per-pair terms over its 64 pixels with one 31-shuffle split butterfly (+ 6 for the ninth terms), and adds
+//     them to a per-batch accumulator in shared memory;
 //   * after a batch the CTA flushes one record per (tile, Gaussian) with two float4 + one scalar global
 //     reductions: ~1 global atomic record per (tile, Gaussian) instead of 9 per (pixel, Gaussian).
 #include "blend_common.cuh"
