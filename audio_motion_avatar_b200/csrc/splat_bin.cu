@@ -355,7 +355,10 @@ __device__ void bitonic_sort_large(uint64_t *__restrict__ g, uint64_t *s, int n,
 //   sort_tiles<1024, 16384, 64>  buckets of 4097..16384 entries (512x512 training views, 500k-Gaussian close-ups):
 //                                192 KB of smem, one CTA per SM; larger buckets still: bitonic network in place in
 //                                global memory with every stride below 16384 done on chunks in shared memory.
-constexpr int SORT_SMALL_T = 256, SORT_SMALL_CAP = 4096, SORT_SMALL_POP = 16;
+constexpr int SORT_SMALL_CAP = 4096;
+#if !AMAV_SORT_GROUPS
+constexpr int SORT_SMALL_T = 256, SORT_SMALL_POP = 16;
+#endif
 constexpr int SORT_LARGE_T = 1024, SORT_LARGE_CAP = 16384, SORT_LARGE_POP = 64;
 constexpr int SORT_MAX_BIN = 48;                     // a depth bin fuller than this sends the tile to the bitonic network
 
